@@ -1,0 +1,187 @@
+/*
+ * qz_cuda.h — C-ABI of libqz_cuda.so: the sm_100a replacement for qdrant/quantization's
+ * native scorers (quantization/cpp/{sse,avx2,neon}.c, built by quantization/build.rs:18-40 and
+ * bound in encoded_vectors_u8.rs:476-489 / encoded_vectors_binary.rs:317-332) plus the scan
+ * loop, top-k, and batch-encode steps that surround them.
+ *
+ * Plain C: opaque handles, pointers and sizes only.  Every function returns a qz_status
+ * (0 = OK) unless stated; nothing throws or aborts across this boundary.  Status codes map
+ * 1:1 onto the reference's EncodingError (quantization/src/lib.rs:18-24).
+ *
+ * Memory contract: `const T* host` arguments are borrowed for the duration of the call.
+ * `*_dev` entry points take DEVICE pointers and are asynchronous on the context's stream
+ * (they exist so that callers with device-resident data, e.g. the benchmark's timed region,
+ * pay no copies).  An index owns a private device copy of the encoded storage; the caller's
+ * EncodedStorage keeps owning the host bytes (get_vector_data / save keep working).
+ *
+ * Encoded queries are byte blobs of qz_query_bytes(index) bytes:
+ *   u8     : [f32 query offset][actual_dim codes]      (EncodedQueryU8, u8.rs:19-22)
+ *   binary : row_bytes packed sign bits                (EncodedBinVector, binary.rs:17-19)
+ *   pq     : n_chunks*256 f32 lookup table             (EncodedQueryPQ, pq.rs:35-37)
+ *
+ * Ordering contract of every top-k in this library: best score first; "best" = largest when
+ * `largest != 0`, else smallest; ties go to the LOWER point id.  Scores compare by their IEEE
+ * bit pattern mapped monotonically (so -0.0 < +0.0).
+ */
+#ifndef QZ_CUDA_H
+#define QZ_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_MSC_VER)
+#define QZ_API __declspec(dllexport)
+#else
+#define QZ_API __attribute__((visibility("default")))
+#endif
+
+typedef int32_t qz_status;
+enum {
+    QZ_OK = 0,
+    QZ_ARGUMENTS = 1, /* EncodingError::ArgumentsError */
+    QZ_ENCODING = 2,  /* EncodingError::EncodingError — CUDA / NCCL failure, text in qz_last_error */
+    QZ_STOPPED = 3,   /* EncodingError::Stopped */
+    QZ_IO = 4         /* EncodingError::IOError */
+};
+
+/* DistanceType, quantization/src/encoded_vectors.rs:6-11 */
+enum { QZ_DOT = 0, QZ_L1 = 1, QZ_L2 = 2 };
+
+/* codec of an index */
+enum { QZ_CODEC_U8 = 0, QZ_CODEC_BIN = 1, QZ_CODEC_PQ = 2 };
+
+typedef struct qz_ctx qz_ctx;     /* one CUDA device + stream + scratch */
+typedef struct qz_index qz_index; /* one shard of an encoded corpus resident in HBM */
+
+/* ---- context ------------------------------------------------------------------------------ */
+
+/* `stream` = an existing cudaStream_t to run on (e.g. the caller's), or NULL to create one. */
+QZ_API qz_status qz_ctx_create(int32_t device, void *stream, qz_ctx **out);
+QZ_API void qz_ctx_destroy(qz_ctx *ctx);
+/* last error text of this context (never NULL); thread-compatible, not thread-safe */
+QZ_API const char *qz_last_error(const qz_ctx *ctx);
+/* text of a failure that happened before a context existed (qz_ctx_create itself) */
+QZ_API const char *qz_last_global_error(void);
+QZ_API qz_status qz_ctx_synchronize(qz_ctx *ctx);
+/* number of kernels of this library launched through `ctx` so far (bench's gpu_launches) */
+QZ_API uint64_t qz_ctx_launch_count(const qz_ctx *ctx);
+QZ_API int32_t qz_ctx_sm_count(const qz_ctx *ctx);
+
+/* ---- u8 scalar quantizer (EncodedVectorsU8, encoded_vectors_u8.rs) ------------------------- */
+
+/* get_actual_dim / get_quantized_vector_size, u8.rs:252-259 */
+QZ_API uint32_t qz_u8_actual_dim(uint32_t dim);
+QZ_API uint32_t qz_u8_row_bytes(uint32_t dim);
+
+/* Make a device-resident index from encoded storage = count rows of
+ * [f32 vector_offset][actual_dim codes] (u8.rs:78-117) and the Metadata scalars (u8.rs:24-31).
+ * `id_base` is added to local row numbers to form point ids (shard of a larger corpus).
+ * `storage` may be NULL: the index is allocated and zero-filled, to be written through
+ * qz_index_storage_dev (e.g. by qz_u8_encode_dev). */
+QZ_API qz_status qz_u8_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t count, uint32_t dim,
+                                    int32_t distance, int32_t invert, float alpha, float offset, float multiplier,
+                                    uint32_t id_base, qz_index **out);
+/* update the Metadata scalars of an existing u8 index (after a device-side encode) */
+QZ_API qz_status qz_u8_index_set_params(qz_index *index, float alpha, float offset, float multiplier);
+
+/* EncodedVectorsU8::encode (u8.rs:34-140): min/max (quantile.rs:5-19), optional quantile cut
+ * (quantile.rs:21-71), codes + per-vector header, and the three Metadata scalars.
+ *   data        count x dim f32, row-major (the reference's orig_data iterator, materialised)
+ *   quantile    NULL = None
+ *   sample_ids  the vectors the quantile cut is computed on; NULL = all when count <= 100000,
+ *               else 100000 distinct ids from an affine permutation keyed by `seed` (the
+ *               reference draws them from a randomly keyed Permutor, quantile.rs:32-34)
+ *   stop        optional flag polled between row chunks; non-zero => QZ_STOPPED (u8.rs:74-76)
+ *   out_storage count * qz_u8_row_bytes(dim) bytes
+ * The host variant streams `data` through the device in chunks; the _dev variant takes device
+ * pointers for data and out (e.g. qz_index_storage_dev) and returns after synchronising. */
+QZ_API qz_status qz_u8_encode(qz_ctx *ctx, const float *data, uint64_t count, uint32_t dim, int32_t distance,
+                              int32_t invert, const float *quantile, const uint64_t *sample_ids, uint64_t n_sample,
+                              uint64_t seed, const volatile int32_t *stop, uint8_t *out_storage, float *alpha,
+                              float *offset, float *multiplier);
+QZ_API qz_status qz_u8_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, int32_t distance,
+                                  int32_t invert, const float *quantile, const uint64_t *sample_ids,
+                                  uint64_t n_sample, uint64_t seed, const volatile int32_t *stop, uint8_t *d_out,
+                                  float *alpha, float *offset, float *multiplier);
+
+/* ---- binary quantizer (EncodedVectorsBin, encoded_vectors_binary.rs) ------------------------- */
+
+/* bytes per row for BitsStoreType u8 (store_bytes = 1, binary.rs:99-116) or u128 (16, :152-159) */
+QZ_API uint32_t qz_bin_row_bytes(uint32_t dim, int32_t store_bytes);
+/* storage = count rows of packed sign bits, bit i at byte i/8 bit i%8 (binary.rs:193-208) */
+QZ_API qz_status qz_bin_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t count, uint32_t dim,
+                                     int32_t store_bytes, int32_t distance, int32_t invert, uint32_t id_base,
+                                     qz_index **out);
+
+/* EncodedVectorsBin::encode (binary.rs:165-208): bit = (v > 0.0) */
+QZ_API qz_status qz_bin_encode(qz_ctx *ctx, const float *data, uint64_t count, uint32_t dim, int32_t store_bytes,
+                               const volatile int32_t *stop, uint8_t *out_storage);
+QZ_API qz_status qz_bin_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim,
+                                   int32_t store_bytes, const volatile int32_t *stop, uint8_t *d_out);
+
+/* ---- product quantizer (EncodedVectorsPQ, encoded_vectors_pq.rs) ------------------------------ */
+
+/* codes = count rows of n_chunks centroid ids (n_chunks = ceil(dim / chunk_size), pq.rs:109-121);
+ * centroids = Metadata.centroids flattened [256][dim] f32 (pq.rs:39-44). */
+QZ_API qz_status qz_pq_index_create(qz_ctx *ctx, const uint8_t *codes, uint64_t count, uint32_t dim,
+                                    uint32_t chunk_size, const float *centroids, int32_t distance, int32_t invert,
+                                    uint32_t id_base, qz_index **out);
+
+/* ---- any index ------------------------------------------------------------------------------ */
+
+QZ_API void qz_index_destroy(qz_index *index);
+QZ_API int32_t qz_index_codec(const qz_index *index);
+QZ_API uint64_t qz_index_count(const qz_index *index);
+QZ_API uint32_t qz_index_row_bytes(const qz_index *index);
+QZ_API uint32_t qz_query_bytes(const qz_index *index);
+/* device pointer of the encoded storage (count * row_bytes bytes, 16-byte aligned) */
+QZ_API void *qz_index_storage_dev(qz_index *index);
+/* copy the encoded storage back to the host (count * row_bytes bytes) */
+QZ_API qz_status qz_index_download(qz_index *index, uint8_t *storage);
+
+/* encode_query (u8.rs:290-329 / binary.rs:288-291 / pq.rs:525-547): `query` = dim f32 on the
+ * host, `out` = qz_query_bytes(index) bytes on the host.  Runs on the device. */
+QZ_API qz_status qz_encode_query(qz_index *index, const float *query, void *out);
+/* device variant: nq queries [nq][dim] f32 -> nq blobs, both device pointers, asynchronous */
+QZ_API qz_status qz_encode_query_dev(qz_index *index, const float *d_queries, uint32_t nq, void *d_out);
+
+/* The fused scan: score every point against one encoded query and keep the k best.
+ * Replaces the caller-side `for i in 0..count { score_point(q, i) }` + BinaryHeap of
+ * demos/src/ann_benchmark_data.rs:150-167.  Host buffers; writes min(k, count) results and
+ * their number to *n_out.  k <= QZ_MAX_K. */
+#define QZ_MAX_K 1024
+QZ_API qz_status qz_scan_topk(qz_index *index, const void *enc_query, uint32_t k, int32_t largest, float *scores,
+                              uint32_t *ids, uint32_t *n_out);
+/* device variant, asynchronous on the context stream: d_enc_query device blob; results as
+ * k sorted u64 keys (d_keys, may be NULL) and/or decoded d_scores/d_ids (may be NULL).
+ * Unfilled slots (count < k) hold key 0 / score NaN / id 0xFFFFFFFF. */
+QZ_API qz_status qz_scan_topk_dev(qz_index *index, const void *d_enc_query, uint32_t k, int32_t largest,
+                                  uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
+
+/* score_point for every point: out[i] = score_point(q, i), i in [0,count). */
+QZ_API qz_status qz_scan_scores(qz_index *index, const void *enc_query, float *scores);
+QZ_API qz_status qz_scan_scores_dev(qz_index *index, const void *d_enc_query, float *d_scores);
+
+/* score_point on an id list (local row numbers): backs EncodedVectors::score_point, n = 1 legal
+ * (u8.rs:331-384, binary.rs:293-300, pq.rs:549-561) */
+QZ_API qz_status qz_score_points(qz_index *index, const void *enc_query, const uint32_t *rows, uint64_t n,
+                                 float *scores);
+/* score_internal on id pairs: backs EncodedVectors::score_internal
+ * (u8.rs:386-453, binary.rs:302-314, pq.rs:566-593) */
+QZ_API qz_status qz_score_pairs(qz_index *index, const uint32_t *rows_a, const uint32_t *rows_b, uint64_t n,
+                                float *scores);
+
+/* Merge `n_lists` best-first top-k lists (e.g. one per shard after an all-gather) into one.
+ * Device pointers, asynchronous: d_keys_in = [n_lists][k] u64 keys as produced by
+ * qz_scan_topk_dev; outputs as in qz_scan_topk_dev. */
+QZ_API qz_status qz_merge_topk_dev(qz_ctx *ctx, const uint64_t *d_keys_in, uint32_t n_lists, uint32_t k,
+                                   int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QZ_CUDA_H */

@@ -1,0 +1,131 @@
+// qz_ctx.cu — context, error plumbing, scratch management (C-ABI of include/qz_cuda.h)
+#include <string.h>
+
+#include "qz_internal.h"
+
+static thread_local std::string g_global_err;
+
+namespace qz {
+
+qz_status fail(qz_ctx *ctx, qz_status st, const std::string &msg) {
+    if (ctx) ctx->err = msg;
+    else g_global_err = msg;
+    return st;
+}
+
+qz_status cuda_fail(qz_ctx *ctx, cudaError_t e, const char *what) {
+    std::string m = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    return fail(ctx, QZ_ENCODING, m);
+}
+
+static qz_status grow_dev(qz_ctx *ctx, uint8_t **p, size_t *have, size_t want) {
+    if (*have >= want) return QZ_OK;
+    size_t n = want < 4096 ? 4096 : want + want / 4;
+    if (*p) {
+        QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        QZ_CUDA(ctx, cudaFree(*p));
+        *p = nullptr;
+        *have = 0;
+    }
+    QZ_CUDA(ctx, cudaMalloc((void **)p, n));
+    *have = n;
+    return QZ_OK;
+}
+
+qz_status ensure_query(qz_ctx *ctx, size_t bytes) { return grow_dev(ctx, &ctx->d_query, &ctx->d_query_bytes, bytes); }
+qz_status ensure_io(qz_ctx *ctx, size_t bytes) { return grow_dev(ctx, &ctx->d_io, &ctx->d_io_bytes, bytes); }
+
+qz_status ensure_pin(qz_ctx *ctx, size_t bytes) {
+    if (ctx->h_pin_bytes >= bytes) return QZ_OK;
+    size_t n = bytes < 65536 ? 65536 : bytes + bytes / 4;
+    if (ctx->h_pin) {
+        QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        QZ_CUDA(ctx, cudaFreeHost(ctx->h_pin));
+        ctx->h_pin = nullptr;
+        ctx->h_pin_bytes = 0;
+    }
+    QZ_CUDA(ctx, cudaMallocHost((void **)&ctx->h_pin, n));
+    ctx->h_pin_bytes = n;
+    return QZ_OK;
+}
+
+}  // namespace qz
+
+using namespace qz;
+
+extern "C" {
+
+qz_status qz_ctx_create(int32_t device, void *stream, qz_ctx **out) {
+    if (!out) return fail(nullptr, QZ_ARGUMENTS, "qz_ctx_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, QZ_ENCODING,
+                    std::string("qz_ctx_create: no CUDA device (") + cudaGetErrorString(e) +
+                        "); libqz_cuda has no CPU fallback");
+    if (device < 0 || device >= n) return fail(nullptr, QZ_ARGUMENTS, "qz_ctx_create: bad device ordinal");
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceProperties");
+    if (prop.major != 10)
+        return fail(nullptr, QZ_ENCODING,
+                    "qz_ctx_create: device is sm_" + std::to_string(prop.major * 10 + prop.minor) +
+                        ", this library contains sm_100a code only");
+    qz_ctx *ctx = new qz_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    e = cudaSetDevice(device);
+    if (e == cudaSuccess) {
+        if (stream) {
+            ctx->stream = (cudaStream_t)stream;
+        } else {
+            e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+            ctx->own_stream = true;
+        }
+    }
+    const size_t lists = ctx->sm_count > 256 ? ctx->sm_count : 256;
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_partial, lists * QZ_MAX_K * sizeof(uint64_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_merge_tmp, (size_t)256 * QZ_MAX_K * sizeof(uint64_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_keys, QZ_MAX_K * sizeof(uint64_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_scores_k, QZ_MAX_K * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_ids_k, QZ_MAX_K * sizeof(uint32_t));
+    if (e != cudaSuccess) {
+        qz_status st = cuda_fail(nullptr, e, "qz_ctx_create");
+        qz_ctx_destroy(ctx);
+        return st;
+    }
+    *out = ctx;
+    return QZ_OK;
+}
+
+void qz_ctx_destroy(qz_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->d_partial);
+    cudaFree(ctx->d_merge_tmp);
+    cudaFree(ctx->d_keys);
+    cudaFree(ctx->d_scores_k);
+    cudaFree(ctx->d_ids_k);
+    cudaFree(ctx->d_query);
+    cudaFree(ctx->d_io);
+    if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *qz_last_error(const qz_ctx *ctx) { return ctx ? ctx->err.c_str() : g_global_err.c_str(); }
+const char *qz_last_global_error(void) { return g_global_err.c_str(); }
+
+qz_status qz_ctx_synchronize(qz_ctx *ctx) {
+    if (!ctx) return QZ_ARGUMENTS;
+    QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return QZ_OK;
+}
+
+uint64_t qz_ctx_launch_count(const qz_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int32_t qz_ctx_sm_count(const qz_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
+
+}  // extern "C"

@@ -1,0 +1,103 @@
+// qz_internal.h — host-side structures behind the opaque handles of include/qz_cuda.h
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <string>
+
+#include "../../include/qz_cuda.h"
+
+struct qz_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    std::string err;
+    uint64_t launches = 0;
+    std::mutex mu;  // serialises host entry points that share the scratch below
+
+    // device scratch
+    uint64_t *d_partial = nullptr;  // [max(sm_count,256)][QZ_MAX_K] per-CTA top-k lists
+    uint64_t *d_merge_tmp = nullptr;
+    uint64_t *d_keys = nullptr;     // [QZ_MAX_K]
+    float *d_scores_k = nullptr;    // [QZ_MAX_K]
+    uint32_t *d_ids_k = nullptr;    // [QZ_MAX_K]
+    uint8_t *d_query = nullptr;     // staged encoded query / f32 query
+    size_t d_query_bytes = 0;
+    uint8_t *d_io = nullptr;        // generic staging (id lists, score arrays)
+    size_t d_io_bytes = 0;
+    // pinned host staging
+    uint8_t *h_pin = nullptr;
+    size_t h_pin_bytes = 0;
+};
+
+struct qz_index {
+    qz_ctx *ctx = nullptr;
+    int codec = 0;
+    uint64_t count = 0;
+    uint32_t dim = 0;
+    uint32_t row_bytes = 0;
+    int distance = 0, invert = 0;
+    uint32_t id_base = 0;
+    uint8_t *d_storage = nullptr;
+    size_t alloc_bytes = 0;
+    // u8 (Metadata, encoded_vectors_u8.rs:24-31)
+    uint32_t actual_dim = 0;
+    float alpha = 0, offset = 0, multiplier = 0;
+    // binary
+    int store = 16;
+    // pq (Metadata, encoded_vectors_pq.rs:39-44)
+    uint32_t n_chunks = 0;
+    float *d_centroids = nullptr;    // [256][dim]
+    uint32_t *d_bounds = nullptr;    // [n_chunks+1]
+    uint32_t *h_bounds = nullptr;
+    float *d_lut_perm = nullptr;     // scratch: bank-permuted LUT of the current query
+    float *d_pq_partial = nullptr;   // scratch: [n_slices][count] partial sums
+    uint32_t pq_slices = 0;
+};
+
+namespace qz {
+
+qz_status fail(qz_ctx *ctx, qz_status st, const std::string &msg);
+qz_status cuda_fail(qz_ctx *ctx, cudaError_t e, const char *what);
+qz_status ensure_query(qz_ctx *ctx, size_t bytes);
+qz_status ensure_io(qz_ctx *ctx, size_t bytes);
+qz_status ensure_pin(qz_ctx *ctx, size_t bytes);
+
+#define QZ_CUDA(ctx, call)                                          \
+    do {                                                            \
+        cudaError_t e__ = (call);                                   \
+        if (e__ != cudaSuccess) return qz::cuda_fail(ctx, e__, #call); \
+    } while (0)
+
+#define QZ_TRY(call)                   \
+    do {                               \
+        qz_status s__ = (call);        \
+        if (s__ != QZ_OK) return s__;  \
+    } while (0)
+
+static inline uint32_t pow2_ceil(uint32_t v) {
+    uint32_t p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+static inline uint32_t topk_pad(uint32_t k) { return pow2_ceil(k < 128 ? 128 : k); }
+
+// scans (row_scan.cu)
+qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, uint32_t k, int largest,
+                          uint32_t *n_lists, uint32_t *Kp_out);
+// merge (topk.cu): lists at d_in -> final keys/scores/ids
+qz_status launch_merge(qz_ctx *ctx, const uint64_t *d_in, uint32_t n_lists, uint32_t in_len, uint32_t in_stride,
+                       uint32_t k, int largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
+
+// point_kernels.cu
+qz_status launch_u8_encode_query(qz_index *ix, const float *d_queries, uint32_t nq, void *d_out);
+qz_status launch_gather(qz_index *ix, const void *d_query, const uint32_t *d_rows_a, const uint32_t *d_rows_b,
+                        uint64_t n, float *d_out);
+qz_status launch_scores_topk(qz_ctx *ctx, const float *d_parts, uint32_t n_parts, uint64_t part_stride, uint64_t n,
+                             float *d_sum_out, uint32_t k, int largest, uint32_t id_base, uint32_t *n_lists,
+                             uint32_t *Kp_out);
+
+}  // namespace qz

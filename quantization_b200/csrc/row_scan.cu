@@ -1,0 +1,172 @@
+// row_scan.cu — host-side planning + launch of row_scan_kernel and merge_lists_kernel
+#include "qz_internal.h"
+#include "row_scan.cuh"
+
+namespace qz {
+
+struct ScanPlan {
+    uint32_t tile_rows, slot_bytes, n_slots, wpl;
+    uint64_t n_tiles;
+    size_t smem;
+};
+
+static const int kWplSet[] = {1, 2, 4, 8, 12, 16, 24, 32};
+
+// Shapes the TMA ring kernel handles: rows that are whole 32-bit words, at most 32*32 code words.
+static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes, uint32_t code_words, uint32_t Kp,
+                          ScanPlan *pl) {
+    if (row_bytes == 0 || row_bytes % 4 != 0 || code_words == 0 || code_words > 32 * 32) return false;
+    const uint32_t target = 24832;  // 16 rows of the 1536-d u8 layout (16*1540 = 24640) rounded to 128
+    uint32_t tile_rows = (target / row_bytes) / kBatchRows * kBatchRows;
+    if (tile_rows < (uint32_t)kBatchRows) tile_rows = kBatchRows;
+    // small corpora: shrink tiles until every SM has ~2 of them
+    const uint64_t want_tiles = 2ull * ctx->sm_count;
+    while (tile_rows > (uint32_t)kBatchRows && (count + tile_rows - 1) / tile_rows < want_tiles) tile_rows -= kBatchRows;
+    uint32_t slot_bytes = (tile_rows * row_bytes + 127) / 128 * 128;
+    const size_t fixed = (size_t)Kp * 8 + (size_t)kConsumerWarps * kCandPerWarp * 8 + 2 * kMaxSlots * 8 + 16;
+    if (ctx->smem_optin < fixed + 2 * (size_t)slot_bytes) return false;
+    uint32_t n_slots = (uint32_t)((ctx->smem_optin - fixed) / slot_bytes);
+    if (n_slots > (uint32_t)kMaxSlots) n_slots = kMaxSlots;
+    uint32_t need = (code_words + 31) / 32;
+    uint32_t wpl = 0;
+    for (int w : kWplSet)
+        if ((uint32_t)w >= need) {
+            wpl = w;
+            break;
+        }
+    if (!wpl) return false;
+    pl->tile_rows = tile_rows;
+    pl->slot_bytes = slot_bytes;
+    pl->n_slots = n_slots;
+    pl->wpl = wpl;
+    pl->n_tiles = (count + tile_rows - 1) / tile_rows;
+    pl->smem = fixed + (size_t)n_slots * slot_bytes;
+    return true;
+}
+
+template <int OP, int WPL>
+static cudaError_t launch_one(const RowScanParams &p, uint32_t grid, size_t smem, cudaStream_t stream) {
+    static bool attr_done = false;  // per instantiation
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(row_scan_kernel<OP, WPL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    row_scan_kernel<OP, WPL><<<grid, kScanThreads, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
+template <int OP>
+static cudaError_t launch_wpl(uint32_t wpl, const RowScanParams &p, uint32_t grid, size_t smem, cudaStream_t s) {
+    switch (wpl) {
+        case 1: return launch_one<OP, 1>(p, grid, smem, s);
+        case 2: return launch_one<OP, 2>(p, grid, smem, s);
+        case 4: return launch_one<OP, 4>(p, grid, smem, s);
+        case 8: return launch_one<OP, 8>(p, grid, smem, s);
+        case 12: return launch_one<OP, 12>(p, grid, smem, s);
+        case 16: return launch_one<OP, 16>(p, grid, smem, s);
+        case 24: return launch_one<OP, 24>(p, grid, smem, s);
+        default: return launch_one<OP, 32>(p, grid, smem, s);
+    }
+}
+
+// Launch the scan of a u8 or binary index.  d_scores (optional) receives every score;
+// if k > 0 the per-CTA top-k lists land in ctx->d_partial ([*n_lists][*Kp_out]).
+// Returns QZ_ARGUMENTS with a message if the row shape is not supported by this kernel.
+qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, uint32_t k, int largest,
+                          uint32_t *n_lists, uint32_t *Kp_out) {
+    qz_ctx *ctx = ix->ctx;
+    const uint32_t Kp = k ? topk_pad(k) : 128;
+    const uint32_t hdr = ix->codec == QZ_CODEC_U8 ? 1 : 0;
+    const uint32_t code_words = ix->row_bytes / 4 - hdr;
+    ScanPlan pl;
+    if (!plan_row_scan(ctx, ix->count, ix->row_bytes, code_words, Kp, &pl))
+        return fail(ctx, QZ_ARGUMENTS, "row shape not supported by the streaming scan kernel");
+    RowScanParams p{};
+    p.storage = ix->d_storage;
+    p.count = ix->count;
+    p.total_bytes16 = (ix->count * (uint64_t)ix->row_bytes + 15) / 16 * 16;
+    p.row_words = ix->row_bytes / 4;
+    p.hdr_words = hdr;
+    p.code_words = code_words;
+    p.tile_rows = pl.tile_rows;
+    p.slot_bytes = pl.slot_bytes;
+    p.n_slots = pl.n_slots;
+    p.n_tiles = pl.n_tiles;
+    p.query = reinterpret_cast<const uint32_t *>(d_query);
+    p.multiplier = ix->multiplier;
+    p.dim = ix->dim;
+    const bool dot = ix->distance == QZ_DOT;
+    p.bin_zx = (dot && !ix->invert) || (!dot && ix->invert);
+    p.scores = d_scores;
+    p.partial = k ? ctx->d_partial : nullptr;
+    p.k = k ? k : 1;
+    p.Kp = Kp;
+    p.flip = largest ? 0u : 0xFFFFFFFFu;
+    p.id_base = ix->id_base;
+    uint32_t grid = (uint32_t)(pl.n_tiles < (uint64_t)ctx->sm_count ? pl.n_tiles : (uint64_t)ctx->sm_count);
+    cudaError_t e;
+    if (ix->codec == QZ_CODEC_BIN) e = launch_wpl<kOpXor>(pl.wpl, p, grid, pl.smem, ctx->stream);
+    else if (ix->distance == QZ_L1) e = launch_wpl<kOpL1>(pl.wpl, p, grid, pl.smem, ctx->stream);
+    else e = launch_wpl<kOpDot>(pl.wpl, p, grid, pl.smem, ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "row_scan_kernel launch");
+    ctx->launches++;
+    if (n_lists) *n_lists = grid;
+    if (Kp_out) *Kp_out = Kp;
+    return QZ_OK;
+}
+
+// Reduce sorted lists to the final top-k.  One launch when everything fits one CTA's shared
+// memory (<= 32768/Kp lists), otherwise a tree of launches through ctx->d_merge_tmp.
+qz_status launch_merge(qz_ctx *ctx, const uint64_t *d_in, uint32_t n_lists, uint32_t in_len, uint32_t in_stride,
+                       uint32_t k, int largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e =
+            cudaFuncSetAttribute(merge_lists_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "merge attr");
+        attr_done = true;
+    }
+    const uint32_t Kp = topk_pad(in_len > k ? in_len : k);
+    const uint32_t max_lists = 32768 / Kp;  // (lists/2)*Kp keys <= 16384
+    const uint64_t *in = d_in;
+    uint64_t *bufs[2] = {ctx->d_merge_tmp, ctx->d_merge_tmp + (size_t)128 * QZ_MAX_K};
+    int which = 0;
+    for (;;) {
+        uint32_t lpc = pow2_ceil(n_lists < 2 ? 2 : n_lists);
+        if (lpc > max_lists) lpc = max_lists;
+        const uint32_t grid = (n_lists + lpc - 1) / lpc;
+        const bool final_level = grid == 1;
+        MergeParams p{};
+        p.in = in;
+        p.n_lists = n_lists;
+        p.in_len = in_len;
+        p.in_stride = in_stride;
+        p.Kp = Kp;
+        p.lists_per_cta = lpc;
+        p.out = final_level ? nullptr : bufs[which];
+        p.out_stride = Kp;
+        p.out_len = Kp;
+        p.final_out = final_level;
+        p.k = k;
+        p.flip = largest ? 0u : 0xFFFFFFFFu;
+        p.keys = d_keys;
+        p.scores = d_scores;
+        p.ids = d_ids;
+        const size_t smem = (size_t)(lpc / 2) * Kp * 8;
+        merge_lists_kernel<0><<<grid, 1024, smem, ctx->stream>>>(p);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "merge_lists_kernel launch");
+        ctx->launches++;
+        if (final_level) break;
+        in = bufs[which];
+        n_lists = grid;
+        in_len = Kp;
+        in_stride = Kp;
+        which ^= 1;
+    }
+    return QZ_OK;
+}
+
+}  // namespace qz

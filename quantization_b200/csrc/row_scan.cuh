@@ -1,0 +1,213 @@
+// row_scan.cuh — the single-query brute-force scan over fixed-size encoded rows.
+//
+// One persistent CTA per SM.  A producer thread streams tiles of `tile_rows` consecutive rows
+// from HBM into a shared-memory ring with 1-D bulk async copies (TMA engine, UBLKCP) that
+// complete on mbarriers; eight consumer warps each take whole tiles.  Inside a tile a warp
+// works on 16 rows at a time: lane l owns 32-bit words l, l+32, ... of every row (bank-conflict
+// free for any row stride, and the matching query words stay in registers), accumulates an
+// exact integer per row, and a 16-shuffle butterfly leaves row r's total in lanes 2r, 2r+1.
+// The epilogue applies the codec's affine map, optionally stores the score, and feeds the fused
+// CTA top-k (topk.cuh).  Rows keep the reference's AoS layout byte for byte, including the
+// 4-byte-misaligned u8 rows (stride = actual_dim + 4): tiles are 16-row multiples so every tile
+// starts 16-byte aligned.
+//
+// Replaces, for the u8 codec: impl_score_dot_* / impl_score_l1_* (quantization/cpp/avx2.c:31-128,
+// sse.c:23-47,108-149) and EncodedVectorsU8::score_point (encoded_vectors_u8.rs:331-384);
+// for the binary codec: impl_xor_popcnt_* (sse.c:49-106) and calculate_metric
+// (encoded_vectors_binary.rs:237-252); plus the caller's scan loop and heap
+// (demos/src/ann_benchmark_data.rs:150-167).
+#pragma once
+#include "common.cuh"
+#include "topk.cuh"
+
+namespace qz {
+
+constexpr int kOpDot = 0, kOpL1 = 1, kOpXor = 2;
+constexpr int kConsumerWarps = 8;
+constexpr int kScanThreads = (kConsumerWarps + 1) * 32;
+constexpr int kMaxSlots = 8;
+constexpr int kBatchRows = 16;
+
+struct RowScanParams {
+    const uint8_t *storage;  // 16-byte aligned, readable up to round_up(count*row_bytes, 16)
+    uint64_t count;
+    uint64_t total_bytes16;  // round_up(count*row_bytes, 16)
+    uint32_t row_words;      // row_bytes / 4
+    uint32_t hdr_words;      // 1 for u8 rows (f32 vector_offset), 0 for binary
+    uint32_t code_words;     // words scored per row
+    uint32_t tile_rows;      // multiple of 16
+    uint32_t slot_bytes;     // >= tile_rows*row_bytes, multiple of 128
+    uint32_t n_slots;
+    uint64_t n_tiles;
+    const uint32_t *query;  // device blob: u8 [f32 offset][codes], binary [bits]
+    float multiplier;       // u8
+    uint32_t dim;           // binary
+    int bin_zx;             // binary: 1 => zeros - xor, 0 => xor - zeros
+    float *scores;          // optional [count]
+    uint64_t *partial;      // optional [gridDim.x][Kp]
+    uint32_t k, Kp, flip, id_base;
+};
+
+template <int OP>
+__device__ __forceinline__ uint32_t scan_op(uint32_t v, uint32_t q, uint32_t acc) {
+    if (OP == kOpDot) return __dp4a(v, q, acc);
+    if (OP == kOpL1) return acc + __vsadu4(v, q);
+    return acc + __popc(v ^ q);
+}
+
+template <int OP, int WPL>
+__global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScanParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *ring = smem;
+    uint64_t *top = reinterpret_cast<uint64_t *>(smem + (size_t)p.n_slots * p.slot_bytes);
+    uint64_t *cand_all = top + p.Kp;
+    uint64_t *full = cand_all + kConsumerWarps * kCandPerWarp;
+    uint64_t *empty = full + kMaxSlots;
+    uint64_t *thr = empty + kMaxSlots;
+    int *lock = reinterpret_cast<int *>(thr + 1);
+
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool do_topk = p.partial != nullptr;
+
+    if (threadIdx.x == 0) {
+        for (uint32_t s = 0; s < p.n_slots; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        *thr = 0;
+        *lock = 0;
+        fence_mbar_init();
+    }
+    if (do_topk)
+        for (uint32_t i = threadIdx.x; i < p.Kp; i += blockDim.x) top[i] = 0;
+    __syncthreads();
+
+    // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const uint64_t my_tiles = (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    const uint64_t tile_bytes = (uint64_t)p.tile_rows * p.row_words * 4;
+
+    if (warp == kConsumerWarps) {
+        // ---------------- producer ----------------
+        if (lane == 0) {
+            const uint64_t pol = l2_policy_evict_first();
+            for (uint64_t t = 0; t < my_tiles; t++) {
+                const uint32_t slot = (uint32_t)(t % p.n_slots);
+                const uint32_t round = (uint32_t)(t / p.n_slots);
+                if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
+                const uint64_t tile = blockIdx.x + t * gridDim.x;
+                const uint64_t off = tile * tile_bytes;
+                uint64_t bytes = p.total_bytes16 - off;
+                if (bytes > tile_bytes) bytes = tile_bytes;
+                mbar_arrive_expect_tx(&full[slot], (uint32_t)bytes);
+                bulk_g2s_hint(ring + (size_t)slot * p.slot_bytes, p.storage + off, (uint32_t)bytes, &full[slot], pol);
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumers ----------------
+    uint32_t q[WPL];
+    bool jv[WPL];
+#pragma unroll
+    for (int j = 0; j < WPL; j++) {
+        const uint32_t w = lane + 32 * j;
+        jv[j] = w < p.code_words;
+        q[j] = jv[j] ? __ldg(p.query + p.hdr_words + w) : 0u;
+    }
+    const float q_off = p.hdr_words ? __uint_as_float(__ldg(p.query)) : 0.0f;
+
+    CtaTopK st{top, thr, lock, p.k, p.Kp};
+    uint64_t *cand = cand_all + warp * kCandPerWarp;
+    int cnt = 0;
+    const uint32_t rw = p.row_words;
+    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2;
+    const uint32_t rr = lane >> 1;
+
+    for (uint64_t t = warp; t < my_tiles; t += kConsumerWarps) {
+        const uint32_t slot = (uint32_t)(t % p.n_slots);
+        const uint32_t parity = (uint32_t)(t / p.n_slots) & 1;
+        mbar_wait(&full[slot], parity);
+        const uint64_t tile = blockIdx.x + t * gridDim.x;
+        const uint64_t row0 = tile * p.tile_rows;
+        const uint32_t rows_valid = (uint32_t)((p.count - row0) < p.tile_rows ? (p.count - row0) : p.tile_rows);
+        const uint32_t *sl = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * p.slot_bytes);
+
+        for (uint32_t b = 0; b < rows_valid; b += kBatchRows) {
+            uint32_t acc[kBatchRows];
+#pragma unroll
+            for (int r = 0; r < kBatchRows; r++) acc[r] = 0;
+            const uint32_t *base = sl + (size_t)b * rw + p.hdr_words + lane;
+#pragma unroll
+            for (int j = 0; j < WPL; j++) {
+                if (jv[j]) {
+#pragma unroll
+                    for (int r = 0; r < kBatchRows; r++) acc[r] = scan_op<OP>(base[r * rw + 32 * j], q[j], acc[r]);
+                }
+            }
+            // butterfly: 16 rows x 32 lanes -> lane pair (2r, 2r+1) holds row r
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                uint32_t keep = upper16 ? acc[i + 8] : acc[i], send = upper16 ? acc[i] : acc[i + 8];
+                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                uint32_t keep = upper8 ? acc[i + 4] : acc[i], send = upper8 ? acc[i] : acc[i + 4];
+                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                uint32_t keep = upper4 ? acc[i + 2] : acc[i], send = upper4 ? acc[i] : acc[i + 2];
+                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            {
+                uint32_t keep = upper2 ? acc[1] : acc[0], send = upper2 ? acc[0] : acc[1];
+                acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            const uint32_t total = acc[0] + __shfl_xor_sync(0xffffffffu, acc[0], 1);
+
+            // epilogue: one row per even lane
+            const uint32_t rit = b + rr;
+            const bool valid = !(lane & 1) && rit < rows_valid;
+            float score;
+            if (OP == kOpXor) {
+                // calculate_metric, encoded_vectors_binary.rs:237-252 (all values small integers, exact)
+                const float x = __uint2float_rn(total);
+                const float z = __fsub_rn(__uint2float_rn(p.dim), x);
+                score = p.bin_zx ? __fsub_rn(z, x) : __fsub_rn(x, z);
+            } else {
+                // multiplier * S + query.offset + vector_offset, left to right, no FMA (u8.rs:347)
+                const float vo = __uint_as_float(sl[(size_t)rit * rw]);
+                score = __fadd_rn(__fadd_rn(__fmul_rn(p.multiplier, __uint2float_rn(total)), q_off), vo);
+            }
+            const uint64_t grow = row0 + rit;
+            if (p.scores && valid) p.scores[grow] = score;
+            if (do_topk) {
+                const uint64_t key = make_key(score, p.id_base + (uint32_t)grow, p.flip);
+                const bool pass = valid && key > *thr;
+                const uint32_t m = __ballot_sync(0xffffffffu, pass);
+                if (m) {
+                    const int n = __popc(m);
+                    if (cnt + n > kCandPerWarp) {
+                        cta_topk_flush(st, cand, cnt, lane);
+                        cnt = 0;
+                    }
+                    if (pass) cand[cnt + __popc(m & ((1u << lane) - 1))] = key;
+                    cnt += n;
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[slot]);
+    }
+
+    if (do_topk) {
+        __syncwarp();
+        if (cnt > 0) cta_topk_flush(st, cand, cnt, lane);
+        named_bar_sync(1, kConsumerWarps * 32);
+        uint64_t *out = p.partial + (size_t)blockIdx.x * p.Kp;
+        for (uint32_t i = threadIdx.x; i < p.Kp; i += kConsumerWarps * 32) out[i] = top[i];
+    }
+}
+
+}  // namespace qz
