@@ -70,6 +70,11 @@ QZ_API qz_status qz_ctx_synchronize(qz_ctx *ctx);
 /* number of kernels of this library launched through `ctx` so far (bench's gpu_launches) */
 QZ_API uint64_t qz_ctx_launch_count(const qz_ctx *ctx);
 QZ_API int32_t qz_ctx_sm_count(const qz_ctx *ctx);
+/* Optional: bracket the dominant scan kernel of every scan call with CUDA events on the context
+ * stream.  qz_ctx_get_timing synchronises and returns the summed kernel time and launch count
+ * since qz_ctx_set_timing (the benchmark's roofline measurement). */
+QZ_API qz_status qz_ctx_set_timing(qz_ctx *ctx, int32_t enabled);
+QZ_API qz_status qz_ctx_get_timing(qz_ctx *ctx, double *total_ms, uint64_t *launches);
 
 /* ---- u8 scalar quantizer (EncodedVectorsU8, encoded_vectors_u8.rs) ------------------------- */
 
@@ -130,6 +135,31 @@ QZ_API qz_status qz_bin_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t co
 QZ_API qz_status qz_pq_index_create(qz_ctx *ctx, const uint8_t *codes, uint64_t count, uint32_t dim,
                                     uint32_t chunk_size, const float *centroids, int32_t distance, int32_t invert,
                                     uint32_t id_base, qz_index **out);
+
+/* find_centroids + kmeans (pq.rs:278-342, kmeans.rs:7-136): 256 centroids per chunk from a sample of
+ * min(10000, count) vectors; all chunks are trained side by side on the device.
+ *   sample_ids     NULL = all ids when count <= 10000, else an affine permutation keyed by `seed`
+ *                  (the reference draws them from a randomly keyed Permutor, pq.rs:300-302)
+ *   max_iterations KMEANS_MAX_ITERATIONS = 100, accuracy KMEANS_ACCURACY = 1e-5 (pq.rs:23-24)
+ *   centroids      out, [256][dim] f32 (host) — Metadata.centroids flattened
+ *   iterations     optional out, [n_chunks]: Lloyd iterations each chunk ran
+ * f64 sums run in point order (= the reference with max_kmeans_threads = 1); an empty cluster is
+ * reseeded from a pseudo-random sample point keyed by `seed` (thread_rng in the reference,
+ * kmeans.rs:111-118).  count <= 256: the points themselves, zero padded (pq.rs:290-297). */
+QZ_API qz_status qz_pq_train(qz_ctx *ctx, const float *data, uint64_t count, uint32_t dim, uint32_t chunk_size,
+                             const uint64_t *sample_ids, uint64_t n_sample, uint64_t seed, uint32_t max_iterations,
+                             float accuracy, const volatile int32_t *stop, float *centroids, uint32_t *iterations);
+QZ_API qz_status qz_pq_train_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, uint32_t chunk_size,
+                                 const uint64_t *sample_ids, uint64_t n_sample, uint64_t seed,
+                                 uint32_t max_iterations, float accuracy, const volatile int32_t *stop,
+                                 float *centroids, uint32_t *iterations);
+/* encode_vector for every row (pq.rs:237-265): per chunk the nearest centroid, strict <, lowest
+ * index wins.  codes = count * n_chunks bytes.  `centroids` is a host pointer in both variants. */
+QZ_API qz_status qz_pq_assign(qz_ctx *ctx, const float *data, uint64_t count, uint32_t dim, uint32_t chunk_size,
+                              const float *centroids, const volatile int32_t *stop, uint8_t *codes);
+QZ_API qz_status qz_pq_assign_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim,
+                                  uint32_t chunk_size, const float *centroids, const volatile int32_t *stop,
+                                  uint8_t *d_codes);
 
 /* ---- any index ------------------------------------------------------------------------------ */
 

@@ -24,6 +24,8 @@ _SIGS = {
     "qz_ctx_synchronize": (C.c_int32, [vp]),
     "qz_ctx_launch_count": (C.c_uint64, [vp]),
     "qz_ctx_sm_count": (C.c_int32, [vp]),
+    "qz_ctx_set_timing": (C.c_int32, [vp, C.c_int32]),
+    "qz_ctx_get_timing": (C.c_int32, [vp, C.POINTER(C.c_double), u64p]),
     "qz_u8_actual_dim": (C.c_uint32, [C.c_uint32]),
     "qz_u8_row_bytes": (C.c_uint32, [C.c_uint32]),
     "qz_u8_index_create": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, C.c_float, C.c_float,
@@ -40,6 +42,12 @@ _SIGS = {
     "qz_bin_encode_dev": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, vp, vp]),
     "qz_pq_index_create": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, vp, C.c_int32, C.c_int32,
                                        C.c_uint32, C.POINTER(vp)]),
+    "qz_pq_train": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, vp, C.c_uint64, C.c_uint64, C.c_uint32,
+                                C.c_float, vp, vp, vp]),
+    "qz_pq_train_dev": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, vp, C.c_uint64, C.c_uint64,
+                                    C.c_uint32, C.c_float, vp, vp, vp]),
+    "qz_pq_assign": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, vp, vp, vp]),
+    "qz_pq_assign_dev": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, vp, vp, vp]),
     "qz_index_destroy": (None, [vp]),
     "qz_index_codec": (C.c_int32, [vp]),
     "qz_index_count": (C.c_uint64, [vp]),

@@ -231,7 +231,9 @@ qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, 
     const uint64_t need = (n_batches + kPqWarps - 1) / kPqWarps;
     if (gx > need) gx = (uint32_t)need;
     dim3 grid(gx, slices);
+    timing_begin(ctx);
     pq_scan_kernel<<<grid, kPqWarps * 32, kSliceFloats * 4, ctx->stream>>>(p);
+    timing_end(ctx);
     QZ_TRY(check_launch(ctx, "pq_scan_kernel"));
     // ordered sum of the slice partials (+ fused top-k lists)
     return launch_scores_topk(ctx, ix->d_pq_partial, slices, ix->count, ix->count, d_scores, k, largest, ix->id_base,

@@ -49,6 +49,38 @@ qz_status ensure_pin(qz_ctx *ctx, size_t bytes) {
     return QZ_OK;
 }
 
+static void timing_drain(qz_ctx *ctx, bool wait) {
+    while (ctx->ev_tail < ctx->ev_head) {
+        const int i = (int)(ctx->ev_tail % qz_ctx::kTimingRing);
+        if (wait) cudaEventSynchronize(ctx->ev_stop[i]);
+        else if (cudaEventQuery(ctx->ev_stop[i]) != cudaSuccess) break;
+        float ms = 0.0f;
+        if (cudaEventElapsedTime(&ms, ctx->ev_start[i], ctx->ev_stop[i]) == cudaSuccess) {
+            ctx->timed_ms += ms;
+            ctx->timed_n++;
+        }
+        ctx->ev_tail++;
+    }
+}
+
+void timing_begin(qz_ctx *ctx) {
+    if (!ctx->timing) return;
+    if (ctx->ev_head - ctx->ev_tail >= (uint64_t)qz_ctx::kTimingRing) timing_drain(ctx, true);
+    const int i = (int)(ctx->ev_head % qz_ctx::kTimingRing);
+    if (!ctx->ev_start[i]) {
+        cudaEventCreate(&ctx->ev_start[i]);
+        cudaEventCreate(&ctx->ev_stop[i]);
+    }
+    cudaEventRecord(ctx->ev_start[i], ctx->stream);
+}
+
+void timing_end(qz_ctx *ctx) {
+    if (!ctx->timing) return;
+    const int i = (int)(ctx->ev_head % qz_ctx::kTimingRing);
+    cudaEventRecord(ctx->ev_stop[i], ctx->stream);
+    ctx->ev_head++;
+}
+
 }  // namespace qz
 
 using namespace qz;
@@ -112,6 +144,10 @@ void qz_ctx_destroy(qz_ctx *ctx) {
     cudaFree(ctx->d_query);
     cudaFree(ctx->d_io);
     if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+    for (int i = 0; i < qz_ctx::kTimingRing; i++) {
+        if (ctx->ev_start[i]) cudaEventDestroy(ctx->ev_start[i]);
+        if (ctx->ev_stop[i]) cudaEventDestroy(ctx->ev_stop[i]);
+    }
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -122,6 +158,23 @@ const char *qz_last_global_error(void) { return g_global_err.c_str(); }
 qz_status qz_ctx_synchronize(qz_ctx *ctx) {
     if (!ctx) return QZ_ARGUMENTS;
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return QZ_OK;
+}
+
+qz_status qz_ctx_set_timing(qz_ctx *ctx, int32_t enabled) {
+    if (!ctx) return QZ_ARGUMENTS;
+    timing_drain(ctx, true);
+    ctx->timing = enabled != 0;
+    ctx->timed_ms = 0.0;
+    ctx->timed_n = 0;
+    return QZ_OK;
+}
+
+qz_status qz_ctx_get_timing(qz_ctx *ctx, double *total_ms, uint64_t *launches) {
+    if (!ctx) return QZ_ARGUMENTS;
+    timing_drain(ctx, true);
+    if (total_ms) *total_ms = ctx->timed_ms;
+    if (launches) *launches = ctx->timed_n;
     return QZ_OK;
 }
 

@@ -31,6 +31,13 @@ struct qz_ctx {
     // pinned host staging
     uint8_t *h_pin = nullptr;
     size_t h_pin_bytes = 0;
+    // optional in-stream timing of the dominant scan kernel (qz_ctx_set_timing)
+    bool timing = false;
+    static constexpr int kTimingRing = 256;
+    cudaEvent_t ev_start[kTimingRing] = {}, ev_stop[kTimingRing] = {};
+    uint64_t ev_head = 0, ev_tail = 0;  // [tail, head) pairs are recorded and not yet read
+    double timed_ms = 0.0;
+    uint64_t timed_n = 0;
 };
 
 struct qz_index {
@@ -65,6 +72,9 @@ qz_status cuda_fail(qz_ctx *ctx, cudaError_t e, const char *what);
 qz_status ensure_query(qz_ctx *ctx, size_t bytes);
 qz_status ensure_io(qz_ctx *ctx, size_t bytes);
 qz_status ensure_pin(qz_ctx *ctx, size_t bytes);
+// bracket the dominant kernel of a scan with events when timing is on
+void timing_begin(qz_ctx *ctx);
+void timing_end(qz_ctx *ctx);
 
 #define QZ_CUDA(ctx, call)                                          \
     do {                                                            \

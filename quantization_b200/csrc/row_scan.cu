@@ -107,9 +107,11 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     p.id_base = ix->id_base;
     uint32_t grid = (uint32_t)(pl.n_tiles < (uint64_t)ctx->sm_count ? pl.n_tiles : (uint64_t)ctx->sm_count);
     cudaError_t e;
+    timing_begin(ctx);
     if (ix->codec == QZ_CODEC_BIN) e = launch_wpl<kOpXor>(pl.wpl, p, grid, pl.smem, ctx->stream);
     else if (ix->distance == QZ_L1) e = launch_wpl<kOpL1>(pl.wpl, p, grid, pl.smem, ctx->stream);
     else e = launch_wpl<kOpDot>(pl.wpl, p, grid, pl.smem, ctx->stream);
+    timing_end(ctx);
     if (e != cudaSuccess) return cuda_fail(ctx, e, "row_scan_kernel launch");
     ctx->launches++;
     if (n_lists) *n_lists = grid;

@@ -97,6 +97,15 @@ class Context:
     def synchronize(self):
         self.check(self._L.qz_ctx_synchronize(self.handle))
 
+    def set_timing(self, enabled=True):
+        self.check(self._L.qz_ctx_set_timing(self.handle, int(enabled)))
+
+    def get_timing(self):
+        """(total ms, launches) of the dominant scan kernel since set_timing"""
+        ms, n = C.c_double(0), C.c_uint64(0)
+        self.check(self._L.qz_ctx_get_timing(self.handle, C.byref(ms), C.byref(n)))
+        return ms.value, int(n.value)
+
     @property
     def launch_count(self):
         return int(self._L.qz_ctx_launch_count(self.handle))

@@ -1,0 +1,156 @@
+"""GPU parity for the binary and product quantizers vs the CPU oracle.
+Binary: bit-exact bytes, popcounts, scores, top-k (shapes of quantization/tests/test_binary.rs:
+dims {0,1,8,33,65,387} for u8 words, {1,387} for u128 words, 128 vectors of +-1).
+PQ: bit-exact codes (given centroids), bit-exact LUT, bit-exact score_point in the x86 order,
+scan sums within 1e-5 relative (different but fixed summation order), k-means within the
+reference's own tolerance (quantization/tests/test_pq.rs: 513 x 65, |score - exact| < 0.05*dim)."""
+import numpy as np
+import pytest
+
+import oracle as O
+import quantization_b200 as qz
+
+pytestmark = pytest.mark.gpu
+DISTS = [qz.DistanceType.Dot, qz.DistanceType.L1, qz.DistanceType.L2]
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+# ------------------------------------------------------------------------------------------ binary
+@pytest.mark.parametrize("store,dim", [(1, 0), (1, 1), (1, 8), (1, 33), (1, 65), (1, 387), (16, 1), (16, 387),
+                                       (16, 1536), (1, 1536), (16, 128), (1, 100)])
+@pytest.mark.parametrize("dist", DISTS)
+@pytest.mark.parametrize("invert", [False, True])
+def test_binary_reference_shapes(ctx, store, dim, dist, invert):
+    count = 128
+    data = O.signs(42, count * dim).reshape(count, dim)
+    query = O.signs(43, dim)
+    vp = qz.VectorParameters(dim, count, dist, invert)
+    g = qz.EncodedVectorsBin.encode(data, qz.VecStorageBuilder(), vp, bits_store_type=store, ctx=ctx)
+    o = O.OracleBin.encode(data, int(dist), invert, store)
+    assert g.row_bytes == o.row_bytes
+    assert np.array_equal(np.asarray(g.encoded_vectors), o.storage)
+    gq, oq = g.encode_query(query), o.encode_query(query)
+    assert np.array_equal(gq, oq)
+    gs = g.score_all(gq)
+    assert np.array_equal(bits(gs), bits(o.scan(oq)))
+    assert np.array_equal(bits(gs), bits(o.scan(oq, use_ref=False)))
+    if dist == qz.DistanceType.Dot and dim:
+        exact = data @ query * (-1 if invert else 1)
+        assert np.abs(gs - exact).max() <= 0.01 * dim  # test_binary.rs:41,69
+    ia = np.arange(count, dtype=np.uint32)
+    ib = (ia * 5 + 1) % count
+    assert np.array_equal(bits(g.score_pairs(ia, ib)), bits(o.score_pairs(ia, ib)))
+    assert np.array_equal(bits(g.score_points(gq, ib)), bits(o.scan(oq))[ib])
+    largest = (dist == qz.DistanceType.Dot) != invert
+    gs_k, gi = g.search_top_k(gq, 20, largest)
+    os_k, oi = o.search(oq, 20, largest)
+    assert np.array_equal(gi, oi) and np.array_equal(bits(gs_k), bits(os_k))
+
+
+def test_binary_massive_ties_large(ctx):
+    """<= dim+1 distinct scores over 200k rows: the id tie-break is load bearing"""
+    count, dim = 200_000, 256
+    data = O.uniform(7, count * dim, -1.0, 1.0).reshape(count, dim)
+    query = O.uniform(8, dim, -1.0, 1.0)
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
+    g = qz.EncodedVectorsBin.encode(data, qz.VecStorageBuilder(), vp, ctx=ctx)
+    o = O.OracleBin.encode(data, 0, False, 16)
+    assert np.array_equal(np.asarray(g.encoded_vectors), o.storage)
+    gq = g.encode_query(query)
+    for k, largest in ((100, True), (1000, True), (100, False)):
+        gs, gi = g.search_top_k(gq, k, largest)
+        os_, oi = o.search(gq, k, largest, threads=4)
+        assert np.array_equal(gi, oi) and np.array_equal(bits(gs), bits(os_))
+
+
+# ---------------------------------------------------------------------------------------------- pq
+def pq_pair(ctx, data, dist, invert, chunk, centroids=None):
+    count, dim = data.shape
+    o = O.OraclePQ.encode(data, int(dist), invert, chunk, centroids=centroids)
+    vp = qz.VectorParameters(dim, count, dist, invert)
+    g = qz.EncodedVectorsPQ.encode(data, qz.VecStorageBuilder(), vp, chunk, 1, ctx=ctx, centroids=o.centroids)
+    return g, o
+
+
+@pytest.mark.parametrize("dist", DISTS)
+@pytest.mark.parametrize("invert", [False, True])
+def test_pq_given_centroids_513x65(ctx, dist, invert):
+    """assignment, LUT and exact-order scoring are bit-exact once the centroids are fixed"""
+    data = O.uniform(42, 513 * 65).reshape(513, 65)
+    query = O.uniform(43, 65)
+    g, o = pq_pair(ctx, data, dist, invert, 1)
+    assert np.array_equal(np.asarray(g.encoded_vectors), o.codes)
+    glut = g.encode_query(query).view(np.float32)
+    olut = o.encode_query(query)
+    assert np.array_equal(bits(glut), bits(olut))
+    rows = np.arange(513, dtype=np.uint32)
+    ref = o.scan(olut)  # x86 order, pq.rs:405-440
+    assert np.array_equal(bits(g.score_points(glut.view(np.uint8), rows)), bits(ref))
+    gs = g.score_all(glut.view(np.uint8))
+    scale = np.abs(olut).reshape(-1, 256).max(1).sum()
+    assert np.abs(gs - ref).max() <= 1e-5 * scale
+    ia, ib = rows, (rows * 11 + 2) % 513
+    assert np.array_equal(bits(g.score_pairs(ia, ib)), bits(o.score_pairs(ia, ib)))
+    exact = {0: data @ query, 1: np.abs(data - query).sum(1), 2: ((data - query) ** 2).sum(1)}[int(dist)]
+    assert np.abs(gs - (-exact if invert else exact)).max() < 0.05 * 65  # test_pq.rs:16-18,48
+
+
+@pytest.mark.parametrize("dim,chunk", [(64, 2), (96, 4), (130, 3), (512, 2), (1536, 2), (100, 8), (48, 16)])
+def test_pq_shapes_topk(ctx, dim, chunk):
+    count = 3000
+    data = O.uniform(dim, count * dim).reshape(count, dim)
+    query = O.uniform(dim + 1, dim)
+    bounds = O.pq_division(dim, chunk)
+    cen = O.uniform(99, 256 * dim).reshape(256, dim)  # arbitrary fixed centroids: parity does not need training
+    g, o = pq_pair(ctx, data, qz.DistanceType.Dot, False, chunk, centroids=cen)
+    assert np.array_equal(np.asarray(g.encoded_vectors), o.codes)
+    glut = g.encode_query(query)
+    olut = o.encode_query(query)
+    assert np.array_equal(bits(glut.view(np.float32)), bits(olut))
+    gs = g.score_all(glut)
+    ref = o.scan(olut)
+    assert np.abs(gs - ref).max() <= 1e-5 * np.abs(ref).max()
+    # top-k must agree with a top-k over the GPU's own scores (ordering contract), ids exact
+    k_s, k_i = g.search_top_k(glut, 50, True)
+    e_s, e_i = O.topk(gs, 50, True)
+    assert np.array_equal(k_i, e_i) and np.array_equal(bits(k_s), bits(e_s))
+    assert bounds.size - 1 == g.row_bytes
+
+
+def test_pq_kmeans_training(ctx):
+    """real k-means on the device (count > 256): reference tolerance + quantization error no worse than
+    the CPU oracle's k-means by more than 2%"""
+    data = O.uniform(42, 2000 * 32).reshape(2000, 32)
+    query = O.uniform(43, 32)
+    vp = qz.VectorParameters(32, 2000, qz.DistanceType.Dot, False)
+    g = qz.EncodedVectorsPQ.encode(data, qz.VecStorageBuilder(), vp, 2, 1, ctx=ctx)
+    o = O.OraclePQ.encode(data, 0, False, 2)
+    gs = g.score_all(g.encode_query(query))
+    assert np.abs(gs - data @ query).max() < 0.05 * 32
+
+    def qerr(cen, codes):
+        rec = np.zeros_like(data)
+        c = np.asarray(codes).reshape(2000, 16)
+        for ch in range(16):
+            rec[:, 2 * ch:2 * ch + 2] = cen[c[:, ch], 2 * ch:2 * ch + 2]
+        return float(((rec - data) ** 2).sum())
+    ge, oe = qerr(g.centroids, g.encoded_vectors), qerr(o.centroids, o.codes)
+    assert ge <= 1.02 * oe
+    # no empty-cluster reseeds on this data => the device k-means is the oracle's, bit for bit
+    assert np.array_equal(bits(g.centroids), bits(o.centroids))
+
+
+def test_pq_few_points_and_empty(ctx):
+    """count <= 256: centroids are the points (pq.rs:290-297); count = 0 (empty_storage.rs)"""
+    data = O.uniform(1, 100 * 8).reshape(100, 8)
+    vp = qz.VectorParameters(8, 100, qz.DistanceType.L2, False)
+    g = qz.EncodedVectorsPQ.encode(data, qz.VecStorageBuilder(), vp, 2, 1, ctx=ctx)
+    assert np.array_equal(g.centroids[:100], data) and not g.centroids[100:].any()
+    s = g.score_all(g.encode_query(data[3]))
+    assert int(np.argmin(s)) == 3
+    vp0 = qz.VectorParameters(8, 0, qz.DistanceType.Dot, False)
+    g0 = qz.EncodedVectorsPQ.encode(np.zeros((0, 8), np.float32), qz.VecStorageBuilder(), vp0, 2, 1, ctx=ctx)
+    assert g0.count == 0 and g0.search_top_k(g0.encode_query(np.zeros(8, np.float32)), 3, True)[1].size == 0
