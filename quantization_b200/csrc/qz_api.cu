@@ -146,7 +146,9 @@ qz_status qz_encode_query_dev(qz_index *ix, const float *d_queries, uint32_t nq,
 }
 
 qz_status qz_encode_query(qz_index *ix, const float *query, void *out) {
-    if (bad_index(ix) || !query || !out) return fail(ix ? ix->ctx : nullptr, QZ_ARGUMENTS, "encode_query: NULL");
+    if (bad_index(ix)) return QZ_ARGUMENTS;
+    if (qz_query_bytes(ix) == 0) return QZ_OK;  // dim 0: nothing to encode
+    if (!query || !out) return fail(ix->ctx, QZ_ARGUMENTS, "encode_query: NULL");
     qz_ctx *ctx = ix->ctx;
     std::lock_guard<std::mutex> g(ctx->mu);
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));

@@ -138,7 +138,7 @@ qz_status launch_merge(qz_ctx *ctx, const uint64_t *d_in, uint32_t n_lists, uint
     for (;;) {
         uint32_t lpc = pow2_ceil(n_lists < 2 ? 2 : n_lists);
         if (lpc > max_lists) lpc = max_lists;
-        const uint32_t grid = (n_lists + lpc - 1) / lpc;
+        const uint32_t grid = n_lists ? (n_lists + lpc - 1) / lpc : 1;
         const bool final_level = grid == 1;
         MergeParams p{};
         p.in = in;
