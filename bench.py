@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py — scored vectors/s of the encoded-vector scan on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload u8|bin|pq] [--impl reference]
+
+A step = one full scan of the rank's shard against one encoded query, fused top-k included, plus
+(N > 1) the all-gather of the per-rank top-k keys over NCCL and the final merge.  Weak scaling:
+every rank holds `--rows` points (default = the workload's BASELINE size), ids offset by rank.
+`value` is timed with CUDA events on device-resident inputs; `e2e` goes through the host-buffer
+C-ABI calls (encode_query + scan_topk) with their H2D / D2H copies inside the timed region.
+The roofline entry times the scan kernel alone with in-stream events (qz_ctx_set_timing).
+`--impl reference` times the reference's own CPU scorers (oracle/_ref, else the oracle port) on
+the host cores over a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (rows per GPU, dim, bytes per row, description)
+    "u8": dict(rows=1_000_000, dim=1536, row_bytes=1540, k=100, dtype="u8",
+               name="EncodedVectorsU8 dot scan, 1M x 1536-d, single query, top-100 (BASELINE config 2)"),
+    "bin": dict(rows=10_000_000, dim=1536, row_bytes=192, k=100, dtype="u1",
+                name="EncodedVectorsBin xor-popcount scan, 10M x 1536-bit, top-100 (BASELINE config 3)"),
+    "pq": dict(rows=1_000_000, dim=1536, row_bytes=768, k=100, dtype="f32",
+               name="EncodedVectorsPQ LUT scan, 1M x 1536-d, chunk 2 (768 codes/vector), top-100 (BASELINE config 4)"),
+}
+METRIC = "scored vectors/s (u8 dot, 1M x 1536)"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="u8", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the workload's BASELINE size)")
+    ap.add_argument("--cpu-sample", type=int, default=200_000, help="rows of the CPU baseline sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------- GPU arm
+def build_index(qz, torch, ctx, wl, rows, rank, dev):
+    """synthetic random embeddings generated on the device (seed 42 + rank) and encoded there"""
+    g = torch.Generator(device=dev)
+    g.manual_seed(42 + rank)
+    dim = wl["dim"]
+    base = rank * rows
+    if wl is WORKLOADS["u8"]:
+        data = torch.rand((rows, dim), generator=g, device=dev, dtype=torch.float32)
+        vp = qz.VectorParameters(dim, rows, qz.DistanceType.Dot, False)
+        ix = qz.EncodedVectorsU8.encode_dev(data.data_ptr(), vp, None, ctx=ctx, id_base=base)
+        del data
+    elif wl is WORKLOADS["bin"]:
+        vp = qz.VectorParameters(dim, rows, qz.DistanceType.Dot, False)
+        ix = qz.EncodedVectorsBin.empty(vp, ctx=ctx, id_base=base)
+        step = 1_000_000
+        for r in range(0, rows, step):
+            n = min(step, rows - r)
+            chunk = torch.rand((n, dim), generator=g, device=dev, dtype=torch.float32) - 0.5  # sign = +-1 w.p. 1/2
+            ix.encode_rows_dev(chunk.data_ptr(), r, n)
+            del chunk
+    else:
+        data = torch.rand((rows, dim), generator=g, device=dev, dtype=torch.float32)
+        vp = qz.VectorParameters(dim, rows, qz.DistanceType.Dot, False)
+        ix = qz.EncodedVectorsPQ.encode_dev(data.data_ptr(), vp, 2, ctx=ctx, id_base=base)
+        del data
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    return ix
+
+
+def host_query(wl):
+    rng = np.random.default_rng(43)
+    q = rng.random(wl["dim"], dtype=np.float32)
+    return q - 0.5 if wl is WORKLOADS["bin"] else q
+
+
+def cpu_baseline(wl, ix, enc_query, sample_rows, k):
+    """the reference's CPU scorers on a bounded sample of THIS run's encoded rows (rank 0), all host
+    cores, plus a parity check of the GPU result on that same sample"""
+    import oracle as O
+    import quantization_b200 as qz
+    n = min(sample_rows, ix.count)
+    rb = ix.row_bytes
+    storage = np.ascontiguousarray(ix.download()[: n * rb])  # first n rows of the device storage
+    cores = os.cpu_count() or 1
+    vp = ix.vector_parameters
+    if wl is WORKLOADS["u8"]:
+        o = O.OracleU8(storage, n, vp.dim, 0, False, ix.alpha, ix.offset, ix.multiplier)
+        run = lambda: o.search(enc_query, k, True, threads=cores)
+        sub = qz.EncodedVectorsU8(ix.ctx, storage, qz.VectorParameters(vp.dim, n, vp.distance_type, vp.invert),
+                                  ix.alpha, ix.offset, ix.multiplier)
+        kind = "reference" if O.ref.available else "port"
+    elif wl is WORKLOADS["bin"]:
+        o = O.OracleBin(storage, n, vp.dim, 16, 0, False)
+        run = lambda: o.search(enc_query, k, True, threads=cores)
+        sub = qz.EncodedVectorsBin(ix.ctx, storage, qz.VectorParameters(vp.dim, n, vp.distance_type, vp.invert))
+        kind = "reference" if O.ref.available else "port"
+    else:
+        o = O.OraclePQ(storage, n, vp.dim, O.pq_division(vp.dim, 2), ix.centroids, 0, False)
+        lut = np.ascontiguousarray(enc_query).view(np.float32)
+        run = lambda: o.search(lut, k, True, threads=cores)
+        sub = qz.EncodedVectorsPQ(ix.ctx, storage, qz.VectorParameters(vp.dim, n, vp.distance_type, vp.invert), 2,
+                                  ix.centroids)
+        kind = "port"  # score_point_sse is Rust-side intrinsics: restated, not compiled from the reference
+    os_, oi = run()  # warm
+    gs, gi = sub.search_top_k(enc_query, k, True)
+    if wl is WORKLOADS["pq"]:
+        parity = bool(np.allclose(gs, os_, rtol=1e-5, atol=0))
+    else:
+        parity = bool(np.array_equal(gi, oi) and np.array_equal(gs.view(np.uint32), os_.view(np.uint32)))
+    sub.close()
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        run()
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= 3.0 and reps >= 3:
+            break
+    return {"value": n * reps / dt, "unit": "vectors/s", "cores": cores, "kind": kind,
+            "sample": f"first {n} rows of rank 0's shard, {reps} full scans + top-{k}, {cores} threads "
+                      f"(contiguous id ranges, per-thread top-k merged), {dt:.1f} s wall",
+            "gpu_topk_matches_cpu_on_sample": parity}
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    import quantization_b200 as qz
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    wl = WORKLOADS[args.workload]
+    rows = args.rows or wl["rows"]
+    k = wl["k"]
+    stream = torch.cuda.current_stream()
+    ctx = qz.Context(local, stream=stream.cuda_stream)
+    ix = build_index(qz, torch, ctx, wl, rows, rank, dev)
+
+    q_host = host_query(wl)
+    enc = ix.encode_query(q_host)                      # host blob through the C-ABI
+    d_enc = torch.from_numpy(enc.copy()).to(dev)       # device-resident copy for the kernel-timed loop
+    d_keys = torch.zeros(k, dtype=torch.int64, device=dev)
+    d_all = torch.zeros(world * k, dtype=torch.int64, device=dev)
+    d_scores = torch.zeros(k, dtype=torch.float32, device=dev)
+    d_ids = torch.zeros(k, dtype=torch.int32, device=dev)
+    L = ctx._L
+    import ctypes as C
+
+    def step_dev():
+        if world == 1:
+            ix.search_top_k_dev(d_enc.data_ptr(), k, True, 0, d_scores.data_ptr(), d_ids.data_ptr())
+        else:
+            ix.search_top_k_dev(d_enc.data_ptr(), k, True, d_keys.data_ptr(), 0, 0)
+            dist.all_gather_into_tensor(d_all, d_keys)
+            ctx.check(L.qz_merge_topk_dev(ctx.handle, C.c_void_p(d_all.data_ptr()), world, k, 1, None,
+                                          C.c_void_p(d_scores.data_ptr()), C.c_void_p(d_ids.data_ptr())))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_dev()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launch_count
+    ctx.set_timing(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_dev()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    kern_ms, kern_n = ctx.get_timing()
+    ctx.set_timing(False)
+    launches = ctx.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    top_ids = d_ids.cpu().numpy().astype(np.uint32)
+
+    # e2e: the host-buffer calls a user of the trait makes, every step: f32 query -> encode_query ->
+    # scan_topk -> (scores, ids) on the host
+    for _ in range(3):
+        ix.search_top_k(ix.encode_query(q_host), k, True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        blob = ix.encode_query(q_host)
+        hs, hi = ix.search_top_k(blob, k, True)
+        if world > 1:  # host-side exchange of the k results per rank, then merge on the device
+            mine = torch.from_numpy(np.concatenate([hs.view(np.uint32), hi]).astype(np.int64)).to(dev)
+            allr = torch.empty(world * mine.numel(), dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(allr, mine)
+            allr.cpu()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    tm = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(tm[0]), float(tm[1])
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        total_rows = rows * world
+        scan_ms = kern_ms / max(kern_n, 1)
+        achieved = rows * wl["row_bytes"] / (scan_ms * 1e-3) / 1e9
+        out = {
+            "metric": METRIC if args.workload == "u8" else f"scored vectors/s ({args.workload} scan)",
+            "value": total_rows * args.steps / (ms * 1e-3), "unit": "vectors/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"],
+            "data": "synthetic: torch.rand embeddings generated and encoded on the device, seed 42 + rank",
+            "config": {"workload": wl["name"], "rows_per_gpu": rows, "dim": wl["dim"], "k": k,
+                       "bytes_per_vector": wl["row_bytes"], "sharding": f"point-id ranges x{world}",
+                       "l2": f"input {rows * wl['row_bytes'] / 1e6:.0f} MB per GPU per step "
+                             + ("exceeds" if rows * wl["row_bytes"] > 126e6 else "FITS IN") + " the 126 MB L2; no flush"},
+            "e2e": {"value": total_rows * args.steps / (e2e_ms * 1e-3), "unit": "vectors/s",
+                    "h2d_bytes_per_step": int(q_host.nbytes + enc.nbytes),
+                    "d2h_bytes_per_step": int(enc.nbytes + k * 8), "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": {"u8": "row_scan_kernel<dot,12>", "bin": "row_scan_kernel<xor,2>",
+                                                     "pq": "pq_scan_kernel"}[args.workload],
+                         "kernel_ms": scan_ms, "kernel_launches_timed": kern_n, "peak_source": peak_src,
+                         "frac_of_nominal_8TBs": achieved / 8000.0},
+            "clocks": clocks,
+            "top1_id": int(top_ids[0]),
+        }
+        if not args.no_cpu:
+            out["cpu_baseline"] = cpu_baseline(wl, ix, enc, args.cpu_sample, k)
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """The reference's own CPU implementation of the path on the host cores: its C scorers compiled
+    unmodified (oracle/_ref) driven by the restated score_point + caller-side top-k, all host threads.
+    Each step = one scan + top-k of a bounded sample (--cpu-sample rows) of the workload's shape."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import oracle as O
+    wl = WORKLOADS[args.workload]
+    n, dim, k = args.cpu_sample, wl["dim"], wl["k"]
+    cores = os.cpu_count() or 1
+    if args.workload == "u8":
+        data = O.uniform(42, n * dim).reshape(n, dim)
+        o = O.OracleU8.encode(data, 0, False)
+        q = o.encode_query(O.uniform(43, dim))
+        run = lambda: o.search(q, k, True, threads=cores)
+        kind = "reference" if O.ref.available else "port"
+    elif args.workload == "bin":
+        data = O.uniform(42, n * dim, -0.5, 0.5).reshape(n, dim)
+        o = O.OracleBin.encode(data, 0, False, 16)
+        q = o.encode_query(O.uniform(43, dim, -0.5, 0.5))
+        run = lambda: o.search(q, k, True, threads=cores)
+        kind = "reference" if O.ref.available else "port"
+    else:
+        data = O.uniform(42, n * dim).reshape(n, dim)
+        cen = data[:256].copy()  # scoring cost does not depend on centroid quality
+        o = O.OraclePQ.encode(data, 0, False, 2, centroids=cen)
+        q = o.encode_query(O.uniform(43, dim))
+        run = lambda: o.search(q, k, True, threads=cores)
+        kind = "port"
+    del data
+    for _ in range(max(args.warmup, 1)):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        run()
+    dt = time.perf_counter() - t0
+    v = n * args.steps / dt
+    sample = (f"{n} x {dim} rows of the workload's shape (encoded by the oracle), {args.steps} scans + top-{k}, "
+              f"{cores} threads")
+    print(json.dumps({
+        "impl": "reference",
+        "metric": METRIC if args.workload == "u8" else f"scored vectors/s ({args.workload} scan)",
+        "value": v, "unit": "vectors/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 1),
+        "ms_per_step": dt * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": wl["dtype"], "data": "synthetic: SplitMix64 uniform embeddings, seed 42",
+        "config": {"workload": wl["name"], "rows_per_step": n, "dim": dim, "k": k, "bytes_per_vector": wl["row_bytes"]},
+        "cpu_baseline": {"value": v, "unit": "vectors/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "vectors/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_gpu(a)

@@ -20,7 +20,8 @@ class EncodedVectorsBin(DeviceIndex):
         self.vector_parameters = vector_parameters
         self.bits_store_type = bits_store_type
         h = C.c_void_p()
-        st = self._L.qz_bin_index_create(ctx.handle, ptr(np.ascontiguousarray(encoded_vectors, np.uint8)),
+        host = np.ascontiguousarray(encoded_vectors, np.uint8) if encoded_vectors is not None else None
+        st = self._L.qz_bin_index_create(ctx.handle, ptr(host),
                                          vector_parameters.count, vector_parameters.dim, bits_store_type,
                                          int(vector_parameters.distance_type), int(vector_parameters.invert), id_base,
                                          C.byref(h))
@@ -46,6 +47,18 @@ class EncodedVectorsBin(DeviceIndex):
             for i in range(vector_parameters.count):
                 storage_builder.push_vector_data(out[i * row:(i + 1) * row])
         return cls(ctx, storage_builder.build(), vector_parameters, bits_store_type, id_base)
+
+    @classmethod
+    def empty(cls, vector_parameters, *, bits_store_type=BITS_STORE_U128, ctx=None, id_base=0):
+        """an index whose (zeroed) device storage is to be filled with encode_rows_dev"""
+        return cls(pick_ctx(ctx), None, vector_parameters, bits_store_type, id_base)
+
+    def encode_rows_dev(self, d_data, first_row, n_rows):
+        """encode n_rows device-resident f32 rows into rows [first_row, first_row + n_rows) of this index"""
+        dst = self.storage_dev + first_row * self.row_bytes
+        self.ctx.check(self._L.qz_bin_encode_dev(self.ctx.handle, C.c_void_p(d_data), n_rows,
+                                                 self.vector_parameters.dim, self.bits_store_type, None,
+                                                 C.c_void_p(dst)))
 
     @staticmethod
     def get_quantized_vector_size_from_params(vector_parameters, bits_store_type=BITS_STORE_U128, ctx=None):

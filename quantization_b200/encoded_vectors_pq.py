@@ -23,7 +23,8 @@ class EncodedVectorsPQ(DeviceIndex):
         self.centroids = np.ascontiguousarray(centroids, np.float32).reshape(CENTROIDS_COUNT, vector_parameters.dim)
         self.vector_division = self.get_vector_division(vector_parameters.dim, chunk_size)
         h = C.c_void_p()
-        st = self._L.qz_pq_index_create(ctx.handle, ptr(np.ascontiguousarray(encoded_vectors, np.uint8)),
+        host = np.ascontiguousarray(encoded_vectors, np.uint8) if encoded_vectors is not None else None
+        st = self._L.qz_pq_index_create(ctx.handle, ptr(host),
                                         vector_parameters.count, vector_parameters.dim, self.chunk_size,
                                         ptr(self.centroids), int(vector_parameters.distance_type),
                                         int(vector_parameters.invert), id_base, C.byref(h))
@@ -58,6 +59,27 @@ class EncodedVectorsPQ(DeviceIndex):
             for i in range(vp.count):
                 storage_builder.push_vector_data(codes[i * n_chunks:(i + 1) * n_chunks])
         return cls(ctx, storage_builder.build(), vp, chunk_size, centroids, id_base)
+
+    @classmethod
+    def encode_dev(cls, d_data, vector_parameters, chunk_size, *, ctx=None, sample_ids=None, seed=0, centroids=None,
+                   id_base=0):
+        """encode() for a [count, dim] f32 matrix resident on the device: k-means and assignment run
+        there and the codes are written straight into the new index."""
+        ctx = pick_ctx(ctx)
+        L = ctx._L
+        vp = vector_parameters
+        sid = np.ascontiguousarray(sample_ids, np.uint64) if sample_ids is not None else None
+        iters = np.zeros(max(cls.get_quantized_vector_size(vp, chunk_size), 1), np.uint32)
+        if centroids is None:
+            centroids = np.zeros((CENTROIDS_COUNT, vp.dim), np.float32)
+            ctx.check(L.qz_pq_train_dev(ctx.handle, C.c_void_p(d_data), vp.count, vp.dim, chunk_size,
+                                        ptr(sid) if sid is not None else None, sid.size if sid is not None else 0, seed,
+                                        KMEANS_MAX_ITERATIONS, KMEANS_ACCURACY, None, ptr(centroids), ptr(iters)))
+        self = cls(ctx, None, vp, chunk_size, centroids, id_base)
+        self.kmeans_iterations = iters
+        ctx.check(L.qz_pq_assign_dev(ctx.handle, C.c_void_p(d_data), vp.count, vp.dim, chunk_size, ptr(self.centroids),
+                                     None, C.c_void_p(self.storage_dev)))
+        return self
 
     @staticmethod
     def get_quantized_vector_size(vector_parameters, chunk_size):

@@ -28,7 +28,8 @@ class EncodedVectorsU8(DeviceIndex):
         self.actual_dim = self.get_actual_dim(vector_parameters)
         self.alpha, self.offset, self.multiplier = np.float32(alpha), np.float32(offset), np.float32(multiplier)
         h = C.c_void_p()
-        st = self._L.qz_u8_index_create(ctx.handle, ptr(np.ascontiguousarray(encoded_vectors, np.uint8)),
+        host = np.ascontiguousarray(encoded_vectors, np.uint8) if encoded_vectors is not None else None
+        st = self._L.qz_u8_index_create(ctx.handle, ptr(host),
                                         vector_parameters.count, vector_parameters.dim,
                                         int(vector_parameters.distance_type), int(vector_parameters.invert),
                                         float(alpha), float(offset), float(multiplier), id_base, C.byref(h))
@@ -60,6 +61,26 @@ class EncodedVectorsU8(DeviceIndex):
             for i in range(vector_parameters.count):
                 storage_builder.push_vector_data(out[i * row:(i + 1) * row])
         return cls(ctx, storage_builder.build(), vector_parameters, a.value, o.value, m.value, id_base)
+
+    @classmethod
+    def encode_dev(cls, d_data, vector_parameters, quantile=None, *, ctx=None, sample_ids=None, seed=0, id_base=0):
+        """encode() for a [count, dim] f32 matrix already resident on the device (`d_data` = device
+        pointer): the codes are written straight into the new index, nothing crosses PCIe."""
+        ctx = pick_ctx(ctx)
+        L = ctx._L
+        self = cls(ctx, None, vector_parameters, 0.0, 0.0, 0.0, id_base)
+        a, o, m = C.c_float(), C.c_float(), C.c_float()
+        q = C.byref(C.c_float(quantile)) if quantile is not None else None
+        sid = np.ascontiguousarray(sample_ids, np.uint64) if sample_ids is not None else None
+        st = L.qz_u8_encode_dev(ctx.handle, C.c_void_p(d_data), vector_parameters.count, vector_parameters.dim,
+                                int(vector_parameters.distance_type), int(vector_parameters.invert),
+                                C.cast(q, _lib.f32p) if q is not None else None, ptr(sid) if sid is not None else None,
+                                sid.size if sid is not None else 0, seed, None, C.c_void_p(self.storage_dev),
+                                C.byref(a), C.byref(o), C.byref(m))
+        ctx.check(st)
+        ctx.check(L.qz_u8_index_set_params(self.handle, a.value, o.value, m.value))
+        self.alpha, self.offset, self.multiplier = np.float32(a.value), np.float32(o.value), np.float32(m.value)
+        return self
 
     @staticmethod
     def get_quantized_vector_size(vector_parameters):
