@@ -40,8 +40,8 @@ METRIC = "scored vectors/s (u8 dot, 1M x 1536)"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="u8", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the workload's BASELINE size)")
@@ -210,7 +210,8 @@ def run_gpu(args):
     wl = WORKLOADS[args.workload]
     rows = args.rows or wl["rows"]
     k = wl["k"]
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)  # a real (non-default) stream shared by torch, NCCL and libqz_cuda
+    torch.cuda.set_stream(stream)
     ctx = qz.Context(local, stream=stream.cuda_stream)
     ix = build_index(qz, torch, ctx, wl, rows, rank, dev)
 
@@ -238,12 +239,14 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        step_dev()
-    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step_dev()
+    barrier()
+    if rank == 0:
+        sampler.lines.clear()  # keep only samples taken under the timed load
     launches0 = ctx.launch_count
     ctx.set_timing(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -257,6 +260,14 @@ def run_gpu(args):
     kern_ms, kern_n = ctx.get_timing()
     ctx.set_timing(False)
     launches = ctx.launch_count - launches0
+    if rank == 0:
+        # nvidia-smi samples every 100 ms: if the timed region was shorter, keep the same load running
+        # (untimed) until a few samples exist, so the clocks reported are clocks under this load
+        t_end = time.perf_counter() + 3.0
+        while world == 1 and len(sampler.lines) < 5 and time.perf_counter() < t_end:
+            for _ in range(50):
+                step_dev()
+            torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
     top_ids = d_ids.cpu().numpy().astype(np.uint32)
 
