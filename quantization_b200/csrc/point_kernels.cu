@@ -40,8 +40,15 @@ __global__ void __launch_bounds__(256) u8_encode_query_kernel(U8QueryParams p) {
         a1 += c;
         a2 += c * c;
     }
-    atomicAdd(&s1, a1);
-    atomicAdd(&s2, a2);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {  // one 64-bit shared atomic per warp, not per thread (CAS loop)
+        a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+        a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&s1, a1);
+        atomicAdd(&s2, a2);
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
         // integer sums equal the reference's sequential f32 sums while they stay below 2^24;

@@ -127,6 +127,8 @@ qz_status launch_merge(qz_ctx *ctx, const uint64_t *d_in, uint32_t n_lists, uint
     if (!attr_done) {
         cudaError_t e =
             cudaFuncSetAttribute(merge_lists_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(prune_merge_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
         if (e != cudaSuccess) return cuda_fail(ctx, e, "merge attr");
         attr_done = true;
     }
@@ -156,8 +158,13 @@ qz_status launch_merge(qz_ctx *ctx, const uint64_t *d_in, uint32_t n_lists, uint
         p.keys = d_keys;
         p.scores = d_scores;
         p.ids = d_ids;
-        const size_t smem = (size_t)(lpc / 2) * Kp * 8;
-        merge_lists_kernel<0><<<grid, 1024, smem, ctx->stream>>>(p);
+        size_t smem = (size_t)(lpc / 2) * Kp * 8;
+        if (final_level && n_lists <= kPruneMaxLists) {
+            if (smem < kPruneSmem) smem = kPruneSmem;
+            prune_merge_kernel<0><<<1, 1024, smem, ctx->stream>>>(p);
+        } else {
+            merge_lists_kernel<0><<<grid, 1024, smem, ctx->stream>>>(p);
+        }
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return cuda_fail(ctx, e, "merge_lists_kernel launch");
         ctx->launches++;

@@ -116,9 +116,20 @@ struct MergeParams {
     uint32_t *ids;
 };
 
-template <int kUnused = 0>
-__global__ void __launch_bounds__(1024, 1) merge_lists_kernel(MergeParams p) {
-    extern __shared__ __align__(16) uint64_t s[];
+// first k keys of s[0..have) -> keys / scores / ids outputs (slots past `have` are empty)
+__device__ __forceinline__ void write_final(const MergeParams &p, const uint64_t *s, uint32_t have) {
+    for (uint32_t i = threadIdx.x; i < p.k; i += blockDim.x) {
+        const uint64_t key = i < have ? s[i] : 0ull;
+        if (p.keys) p.keys[i] = key;
+        float sc;
+        uint32_t id;
+        split_key(key, p.flip, sc, id);
+        if (p.scores) p.scores[i] = sc;
+        if (p.ids) p.ids[i] = id;
+    }
+}
+
+__device__ __forceinline__ void tree_merge(const MergeParams &p, uint64_t *s) {
     const uint32_t tid = threadIdx.x, T = blockDim.x;
     const uint32_t Kp = p.Kp, half = Kp >> 1;
     const uint32_t first = blockIdx.x * p.lists_per_cta;
@@ -158,17 +169,153 @@ __global__ void __launch_bounds__(1024, 1) merge_lists_kernel(MergeParams p) {
     if (p.out) {
         for (uint32_t i = tid; i < p.out_len; i += T) p.out[(size_t)blockIdx.x * p.out_stride + i] = i < Kp ? s[i] : 0ull;
     }
-    if (p.final_out) {
-        for (uint32_t i = tid; i < p.k; i += T) {
-            uint64_t key = i < Kp ? s[i] : 0ull;
-            if (p.keys) p.keys[i] = key;
-            float sc;
-            uint32_t id;
-            split_key(key, p.flip, sc, id);
-            if (p.scores) p.scores[i] = sc;
-            if (p.ids) p.ids[i] = id;
+    if (p.final_out) write_final(p, s, Kp);
+}
+
+template <int kUnused = 0>
+__global__ void __launch_bounds__(1024, 1) merge_lists_kernel(MergeParams p) {
+    extern __shared__ __align__(16) uint64_t s[];
+    tree_merge(p, s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Final merge with pruning (one CTA).  The lists are sorted, so for any position j the m-th
+// largest of {list_g[j]} has at least m*(j+1) elements at or above it: with m*(j+1) >= k that is
+// a lower bound T on the k-th best key overall.  Only keys >= T (typically a few hundred out of
+// n_lists*k) are gathered and bitonic-sorted.  If more than kPruneCap survive (adversarial
+// inputs) the exact tree merge above runs instead, in the same launch.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kPruneCap = 2048;
+constexpr uint32_t kPruneMaxLists = 256;
+
+// dynamic shared memory the pruned path needs: sort area + staged survivors + their ranks
+constexpr size_t kPruneSmem = (size_t)kPruneCap * (8 + 8 + 4);
+
+template <int kUnused = 0>
+__global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
+    extern __shared__ __align__(16) uint64_t s[];  // max(kPruneSmem, tree-merge need)
+    __shared__ uint64_t vals[kPruneMaxLists];
+    __shared__ uint32_t ranks[kPruneMaxLists];
+    __shared__ uint64_t wmax[kPruneMaxLists / 32];
+    __shared__ uint64_t thrA;
+    __shared__ uint32_t cnt;
+    uint64_t *cand = s + kPruneCap;
+    uint32_t *rk = reinterpret_cast<uint32_t *>(cand + kPruneCap);
+    const uint32_t tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t G = p.n_lists;
+    // probe A: position jp1-1 and the m-th largest value there, m*jp1 >= k, m <= G
+    // probe B: position k-1, m = 1 (the best list's k-th key)
+    const uint32_t m0 = G < p.k ? G : p.k;
+    const uint32_t jp1 = m0 ? (p.k + m0 - 1) / m0 : 1;
+    const uint32_t m = (p.k + jp1 - 1) / jp1;
+    const bool probeA = G > 0 && jp1 <= p.in_len && m <= G;
+    const bool probeB = G > 0 && p.k <= p.in_len;
+    if (tid == 0) {
+        thrA = 0ull;
+        cnt = 0;
+    }
+    if (tid < kPruneMaxLists) {
+        uint64_t a = 0, b = 0;
+        if (tid < G) {
+            if (probeA) a = p.in[(size_t)tid * p.in_stride + (jp1 - 1)];
+            if (probeB) b = p.in[(size_t)tid * p.in_stride + (p.k - 1)];
+        }
+        vals[tid] = a;
+        ranks[tid] = 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint64_t b2 = __shfl_xor_sync(0xffffffffu, b, o);
+            b = b2 > b ? b2 : b;
+        }
+        if (lane == 0) wmax[warp] = b;
+    }
+    __syncthreads();
+    uint64_t thrB = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < kPruneMaxLists / 32; w++) thrB = wmax[w] > thrB ? wmax[w] : thrB;
+    if (probeA) {  // rank every probe value; the comparison loop is split over T / Gp threads per value
+        uint32_t Gp = 32;
+        while (Gp < G) Gp <<= 1;
+        const uint32_t parts = T / Gp, g = tid % Gp, part = tid / Gp;
+        if (g < G) {
+            const uint64_t mine = vals[g];
+            const uint32_t per = (G + parts - 1) / parts;
+            const uint32_t h0 = part * per, h1 = min(h0 + per, G);
+            uint32_t r = 0;
+            for (uint32_t h = h0; h < h1; h++) {
+                const uint64_t v = vals[h];
+                r += (v > mine) || (v == mine && h < g);
+            }
+            if (r) atomicAdd(&ranks[g], r);
+        }
+        __syncthreads();
+        if (tid < G && ranks[tid] == m - 1) thrA = vals[tid];
+    }
+    __syncthreads();
+    const uint64_t Tkey = thrA > thrB ? thrA : thrB;
+    // the survivors of a sorted list are a prefix: one warp per list, 32 positions per step
+    for (uint32_t l = warp; l < G; l += T / 32) {
+        const uint64_t *lp = p.in + (size_t)l * p.in_stride;
+        for (uint32_t i0 = 0; i0 < p.in_len; i0 += 32) {
+            const uint32_t i = i0 + lane;
+            const uint64_t key = i < p.in_len ? lp[i] : 0ull;
+            const bool pass = key != 0 && key >= Tkey;
+            const uint32_t mk = __ballot_sync(0xffffffffu, pass);
+            if (mk) {
+                uint32_t pos0 = 0;
+                if (lane == 0) pos0 = atomicAdd(&cnt, (uint32_t)__popc(mk));
+                pos0 = __shfl_sync(0xffffffffu, pos0, 0);
+                const uint32_t pos = pos0 + __popc(mk & ((1u << lane) - 1));
+                if (pass && pos < kPruneCap) cand[pos] = key;
+            }
+            if (mk != 0xffffffffu) break;
         }
     }
+    __syncthreads();
+    const uint32_t n = cnt;
+    if (n > kPruneCap) {  // not prunable: the exact tree merge, in the same launch (uniform branch)
+        tree_merge(p, s);
+        return;
+    }
+    if (n <= 512) {
+        // rank sort: survivor e goes to slot #{survivors greater than it} (keys are unique)
+        for (uint32_t i = tid; i < kPruneCap; i += T) {
+            if (i < p.k) s[i] = 0ull;
+            if (i < 512) rk[i] = 0;
+        }
+        __syncthreads();
+        uint32_t np = 32;
+        while (np < n) np <<= 1;
+        const uint32_t parts = T / np, e = tid % np, part = tid / np;
+        if (e < n) {
+            const uint64_t mine = cand[e];
+            const uint32_t per = (n + parts - 1) / parts;
+            const uint32_t h0 = part * per, h1 = min(h0 + per, n);
+            uint32_t r = 0;
+            for (uint32_t h = h0; h < h1; h++) r += cand[h] > mine;
+            if (r) atomicAdd(&rk[e], r);
+        }
+        __syncthreads();
+        if (tid < n && rk[tid] < p.k) s[rk[tid]] = cand[tid];
+        __syncthreads();
+        write_final(p, s, p.k);
+        return;
+    }
+    uint32_t P = 1024;
+    while (P < n) P <<= 1;
+    for (uint32_t i = tid; i < P; i += T) s[i] = i < n ? cand[i] : 0ull;
+    __syncthreads();
+    for (uint32_t size = 2; size <= P; size <<= 1) {
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            for (uint32_t t = tid; t < (P >> 1); t += T) {
+                const uint32_t lo = 2 * t - (t & (stride - 1));
+                if ((lo & size) == 0 || size == P) ce_desc(s, (int)lo, (int)(lo + stride));
+                else ce_asc(s, (int)lo, (int)(lo + stride));
+            }
+            __syncthreads();
+        }
+    }
+    write_final(p, s, P);
 }
 
 }  // namespace qz
