@@ -258,6 +258,13 @@ def bin_row_bytes(dim, store=16):
     return int(_lib.qzo_bin_row_bytes(C.c_uint32(dim), C.c_int(store)))
 
 
+def bin_xor_popcnt(a, b):
+    """xor_popcnt over two equal-length byte rows (binary.rs:44-97, 119-150), scalar restatement"""
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return int(_lib.qzo_bin_xor_popcnt(_p(a, _u8p), _p(b, _u8p), C.c_uint32(a.size)))
+
+
 class OracleBin:
     """EncodedVectorsBin (encoded_vectors_binary.rs:11-315) restated on the CPU."""
 
