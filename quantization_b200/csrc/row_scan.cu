@@ -1,4 +1,6 @@
 // row_scan.cu — host-side planning + launch of row_scan_kernel and merge_lists_kernel
+#include <stdlib.h>
+
 #include "qz_internal.h"
 #include "row_scan.cuh"
 
@@ -6,27 +8,42 @@ namespace qz {
 
 struct ScanPlan {
     uint32_t tile_rows, slot_bytes, n_slots, wpl;
-    uint64_t n_tiles;
+    uint32_t n_tiles;
+    bool full;
     size_t smem;
 };
 
-static const int kWplSet[] = {1, 2, 4, 8, 12, 16, 24, 32};
+cudaError_t launch_row_scan_dot(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
+cudaError_t launch_row_scan_l1(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
+cudaError_t launch_row_scan_xor(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
+
+static const int kWplSet[] = {1, 2, 3, 4, 6, 8, 12, 16, 24, 32};
 
 // Shapes the TMA ring kernel handles: rows that are whole 32-bit words, at most 32*32 code words.
+// Ring geometry: slots of ~24 KB (16 rows of the 1536-d u8 layout); the slot count is a power of two
+// (16 / n_slots consumer warps are bound to each slot).  hbm_probe (profiles/r1_hbm_probe.txt): 4-8
+// slots of 24 KB per SM sustain 7.0-7.3 TB/s of bulk copies; many small slots do not.
 static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes, uint32_t code_words, uint32_t Kp,
                           ScanPlan *pl) {
     if (row_bytes == 0 || row_bytes % 4 != 0 || code_words == 0 || code_words > 32 * 32) return false;
-    const uint32_t target = 24832;  // 16 rows of the 1536-d u8 layout (16*1540 = 24640) rounded to 128
-    uint32_t tile_rows = (target / row_bytes) / kBatchRows * kBatchRows;
-    if (tile_rows < (uint32_t)kBatchRows) tile_rows = kBatchRows;
+    if (count >= 0xFFFFFFFFull) return false;
+    static const uint32_t env_target = getenv("QZ_SCAN_TILE_BYTES") ? atoi(getenv("QZ_SCAN_TILE_BYTES")) : 0;
+    static const uint32_t env_align = getenv("QZ_SCAN_ROW_ALIGN") ? atoi(getenv("QZ_SCAN_ROW_ALIGN")) : 0;
+    static const uint32_t env_slots = getenv("QZ_SCAN_SLOTS") ? atoi(getenv("QZ_SCAN_SLOTS")) : 0;
+    const uint32_t target = env_target ? env_target : 24832;
+    const uint32_t align = env_align ? env_align : kTileRowAlign;
+    uint32_t tile_rows = (target / row_bytes) / align * align;
+    if (tile_rows < align) tile_rows = align;
     // small corpora: shrink tiles until every SM has ~2 of them
     const uint64_t want_tiles = 2ull * ctx->sm_count;
-    while (tile_rows > (uint32_t)kBatchRows && (count + tile_rows - 1) / tile_rows < want_tiles) tile_rows -= kBatchRows;
+    while (tile_rows > align && (count + tile_rows - 1) / tile_rows < want_tiles) tile_rows -= align;
     uint32_t slot_bytes = (tile_rows * row_bytes + 127) / 128 * 128;
     const size_t fixed = (size_t)Kp * 8 + (size_t)kConsumerWarps * kCandPerWarp * 8 + 2 * kMaxSlots * 8 + 16;
-    if (ctx->smem_optin < fixed + 2 * (size_t)slot_bytes) return false;
-    uint32_t n_slots = (uint32_t)((ctx->smem_optin - fixed) / slot_bytes);
-    if (n_slots > (uint32_t)kMaxSlots) n_slots = kMaxSlots;
+    if (ctx->smem_optin < fixed + (size_t)slot_bytes) return false;
+    uint32_t fit = (uint32_t)((ctx->smem_optin - fixed) / slot_bytes);
+    uint32_t n_slots = 1;
+    const uint32_t max_slots = env_slots ? env_slots : 8;
+    while (n_slots * 2 <= fit && n_slots * 2 <= max_slots) n_slots *= 2;
     uint32_t need = (code_words + 31) / 32;
     uint32_t wpl = 0;
     for (int w : kWplSet)
@@ -39,36 +56,10 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
     pl->slot_bytes = slot_bytes;
     pl->n_slots = n_slots;
     pl->wpl = wpl;
-    pl->n_tiles = (count + tile_rows - 1) / tile_rows;
+    pl->full = code_words == 32 * wpl;
+    pl->n_tiles = (uint32_t)((count + tile_rows - 1) / tile_rows);
     pl->smem = fixed + (size_t)n_slots * slot_bytes;
     return true;
-}
-
-template <int OP, int WPL>
-static cudaError_t launch_one(const RowScanParams &p, uint32_t grid, size_t smem, cudaStream_t stream) {
-    static bool attr_done = false;  // per instantiation
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(row_scan_kernel<OP, WPL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)227 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
-    row_scan_kernel<OP, WPL><<<grid, kScanThreads, smem, stream>>>(p);
-    return cudaGetLastError();
-}
-
-template <int OP>
-static cudaError_t launch_wpl(uint32_t wpl, const RowScanParams &p, uint32_t grid, size_t smem, cudaStream_t s) {
-    switch (wpl) {
-        case 1: return launch_one<OP, 1>(p, grid, smem, s);
-        case 2: return launch_one<OP, 2>(p, grid, smem, s);
-        case 4: return launch_one<OP, 4>(p, grid, smem, s);
-        case 8: return launch_one<OP, 8>(p, grid, smem, s);
-        case 12: return launch_one<OP, 12>(p, grid, smem, s);
-        case 16: return launch_one<OP, 16>(p, grid, smem, s);
-        case 24: return launch_one<OP, 24>(p, grid, smem, s);
-        default: return launch_one<OP, 32>(p, grid, smem, s);
-    }
 }
 
 // Launch the scan of a u8 or binary index.  d_scores (optional) receives every score;
@@ -85,7 +76,7 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
         return fail(ctx, QZ_ARGUMENTS, "row shape not supported by the streaming scan kernel");
     RowScanParams p{};
     p.storage = ix->d_storage;
-    p.count = ix->count;
+    p.count = (uint32_t)ix->count;
     p.total_bytes16 = (ix->count * (uint64_t)ix->row_bytes + 15) / 16 * 16;
     p.row_words = ix->row_bytes / 4;
     p.hdr_words = hdr;
@@ -105,12 +96,12 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     p.Kp = Kp;
     p.flip = largest ? 0u : 0xFFFFFFFFu;
     p.id_base = ix->id_base;
-    uint32_t grid = (uint32_t)(pl.n_tiles < (uint64_t)ctx->sm_count ? pl.n_tiles : (uint64_t)ctx->sm_count);
+    uint32_t grid = pl.n_tiles < (uint32_t)ctx->sm_count ? pl.n_tiles : (uint32_t)ctx->sm_count;
     cudaError_t e;
     timing_begin(ctx);
-    if (ix->codec == QZ_CODEC_BIN) e = launch_wpl<kOpXor>(pl.wpl, p, grid, pl.smem, ctx->stream);
-    else if (ix->distance == QZ_L1) e = launch_wpl<kOpL1>(pl.wpl, p, grid, pl.smem, ctx->stream);
-    else e = launch_wpl<kOpDot>(pl.wpl, p, grid, pl.smem, ctx->stream);
+    if (ix->codec == QZ_CODEC_BIN) e = launch_row_scan_xor(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
+    else if (ix->distance == QZ_L1) e = launch_row_scan_l1(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
+    else e = launch_row_scan_dot(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
     timing_end(ctx);
     if (e != cudaSuccess) return cuda_fail(ctx, e, "row_scan_kernel launch");
     ctx->launches++;

@@ -2,10 +2,13 @@
 //
 // One persistent CTA per SM.  A producer thread streams tiles of `tile_rows` consecutive rows
 // from HBM into a shared-memory ring with 1-D bulk async copies (TMA engine, UBLKCP) that
-// complete on mbarriers; eight consumer warps each take whole tiles.  Inside a tile a warp
-// works on 16 rows at a time: lane l owns 32-bit words l, l+32, ... of every row (bank-conflict
-// free for any row stride, and the matching query words stay in registers), accumulates an
-// exact integer per row, and a 16-shuffle butterfly leaves row r's total in lanes 2r, 2r+1.
+// complete on mbarriers; sixteen consumer warps drain it, 16 / n_slots warps per slot (a warp
+// is bound to one slot for the whole kernel, so there is no slot arithmetic in the loop).  A
+// warp works on 8 rows at a time: lane l owns 32-bit words l, l+32, ... of every row
+// (bank-conflict free for any row stride, and the matching query words stay in registers),
+// accumulates an exact integer per row, and a 9-shuffle butterfly leaves row r's total in a
+// group of 4 lanes.  (v1 used 8 warps x 16-row batches and was consumer-latency bound at
+// 5.7 TB/s: ~10 cycles between issues per warp; see DESIGN.md.)
 // The epilogue applies the codec's affine map, optionally stores the score, and feeds the fused
 // CTA top-k (topk.cuh).  Rows keep the reference's AoS layout byte for byte, including the
 // 4-byte-misaligned u8 rows (stride = actual_dim + 4): tiles are 16-row multiples so every tile
@@ -23,22 +26,24 @@
 namespace qz {
 
 constexpr int kOpDot = 0, kOpL1 = 1, kOpXor = 2;
-constexpr int kConsumerWarps = 8;
+constexpr int kConsumerWarps = 16;
 constexpr int kScanThreads = (kConsumerWarps + 1) * 32;
-constexpr int kMaxSlots = 8;
-constexpr int kBatchRows = 16;
+constexpr int kMaxSlots = 16;
+constexpr int kBatchRows = 8;    // rows one warp scores per step
+constexpr int kWarmRows = 512;    // rows per CTA scored before the first top-k threshold exists
+constexpr int kTileRowAlign = 16;  // tiles are 16-row multiples => every tile starts 16-byte aligned
 
 struct RowScanParams {
     const uint8_t *storage;  // 16-byte aligned, readable up to round_up(count*row_bytes, 16)
-    uint64_t count;
+    uint32_t count;          // rows (point ids are u32, so count < 2^32)
     uint64_t total_bytes16;  // round_up(count*row_bytes, 16)
     uint32_t row_words;      // row_bytes / 4
     uint32_t hdr_words;      // 1 for u8 rows (f32 vector_offset), 0 for binary
     uint32_t code_words;     // words scored per row
     uint32_t tile_rows;      // multiple of 16
     uint32_t slot_bytes;     // >= tile_rows*row_bytes, multiple of 128
-    uint32_t n_slots;
-    uint64_t n_tiles;
+    uint32_t n_slots;        // power of two, <= 16
+    uint32_t n_tiles;
     const uint32_t *query;  // device blob: u8 [f32 offset][codes], binary [bits]
     float multiplier;       // u8
     uint32_t dim;           // binary
@@ -55,7 +60,9 @@ __device__ __forceinline__ uint32_t scan_op(uint32_t v, uint32_t q, uint32_t acc
     return acc + __popc(v ^ q);
 }
 
-template <int OP, int WPL>
+// WPL = 32-bit words per lane per row (ceil(code_words / 32)); FULL = code_words == 32 * WPL, so no
+// lane ever needs masking.
+template <int OP, int WPL, bool FULL>
 __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScanParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *ring = smem;
@@ -68,11 +75,13 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool do_topk = p.partial != nullptr;
+    const uint32_t n_slots = p.n_slots;
+    const uint32_t warps_per_slot = kConsumerWarps / n_slots;
 
     if (threadIdx.x == 0) {
-        for (uint32_t s = 0; s < p.n_slots; s++) {
+        for (uint32_t s = 0; s < n_slots; s++) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], 1);
+            mbar_init(&empty[s], warps_per_slot);
         }
         *thr = 0;
         *lock = 0;
@@ -82,36 +91,39 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
         for (uint32_t i = threadIdx.x; i < p.Kp; i += blockDim.x) top[i] = 0;
     __syncthreads();
 
-    // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
-    const uint64_t my_tiles = (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
-    const uint64_t tile_bytes = (uint64_t)p.tile_rows * p.row_words * 4;
+    // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...; local tile t lives in slot t % n_slots
+    const uint32_t my_tiles = (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    const uint32_t tile_bytes = p.tile_rows * p.row_words * 4;
 
     if (warp == kConsumerWarps) {
-        // ---------------- producer ----------------
+        // ---------------- producer: one thread feeds the ring with 1-D bulk copies ----------------
         if (lane == 0) {
             const uint64_t pol = l2_policy_evict_first();
-            for (uint64_t t = 0; t < my_tiles; t++) {
-                const uint32_t slot = (uint32_t)(t % p.n_slots);
-                const uint32_t round = (uint32_t)(t / p.n_slots);
+            uint32_t slot = 0, round = 0;
+            uint64_t off = (uint64_t)blockIdx.x * tile_bytes;
+            const uint64_t step = (uint64_t)gridDim.x * tile_bytes;
+            for (uint32_t t = 0; t < my_tiles; t++, off += step) {
                 if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
-                const uint64_t tile = blockIdx.x + t * gridDim.x;
-                const uint64_t off = tile * tile_bytes;
                 uint64_t bytes = p.total_bytes16 - off;
                 if (bytes > tile_bytes) bytes = tile_bytes;
                 mbar_arrive_expect_tx(&full[slot], (uint32_t)bytes);
                 bulk_g2s_hint(ring + (size_t)slot * p.slot_bytes, p.storage + off, (uint32_t)bytes, &full[slot], pol);
+                if (++slot == n_slots) {
+                    slot = 0;
+                    round++;
+                }
             }
         }
         return;
     }
 
-    // ---------------- consumers ----------------
+    // ---------------- consumers: warps_per_slot warps share each slot ----------------
     uint32_t q[WPL];
     bool jv[WPL];
 #pragma unroll
     for (int j = 0; j < WPL; j++) {
         const uint32_t w = lane + 32 * j;
-        jv[j] = w < p.code_words;
+        jv[j] = FULL || w < p.code_words;
         q[j] = jv[j] ? __ldg(p.query + p.hdr_words + w) : 0u;
     }
     const float q_off = p.hdr_words ? __uint_as_float(__ldg(p.query)) : 0.0f;
@@ -120,55 +132,88 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     uint64_t *cand = cand_all + warp * kCandPerWarp;
     int cnt = 0;
     const uint32_t rw = p.row_words;
-    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2;
-    const uint32_t rr = lane >> 1;
+    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4;
+    const uint32_t rr = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);  // row this lane reports
+    const uint32_t slot = warp / warps_per_slot, member = warp - slot * warps_per_slot;
+    const uint32_t *sl = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * p.slot_bytes);
+    const uint32_t batch_stride = warps_per_slot * kBatchRows;
 
-    for (uint64_t t = warp; t < my_tiles; t += kConsumerWarps) {
-        const uint32_t slot = (uint32_t)(t % p.n_slots);
-        const uint32_t parity = (uint32_t)(t / p.n_slots) & 1;
+    // Top-k warm-up (k <= 128): the keys of the CTA's first `warm_tiles` tiles go unfiltered into the
+    // staging area (one slot per row, no atomics); then the consumer warps together reduce them to
+    // the CTA's first sorted list and threshold.  Without this every warp starts with threshold 0,
+    // fills its 128-entry buffer within 16 steps and the 16 lock-serialised flushes that follow
+    // stall the whole ring (measured: +80 us on a 218 us scan).
+    const bool coop = do_topk && p.Kp == (uint32_t)kCandPerWarp;
+    uint32_t warm_rounds = 0;
+    if (coop && n_slots * p.tile_rows <= (uint32_t)(kConsumerWarps * kCandPerWarp)) {
+        const uint32_t per_round = n_slots * p.tile_rows;
+        warm_rounds = (kWarmRows + per_round - 1) / per_round;
+        if (warm_rounds * per_round > (uint32_t)(kConsumerWarps * kCandPerWarp))
+            warm_rounds = (kConsumerWarps * kCandPerWarp) / per_round;
+    }
+
+    uint32_t parity = 0, round = 0;
+    bool warm = warm_rounds > 0;
+    for (uint32_t t = slot;; t += n_slots, parity ^= 1, round++) {
+        if (warm && round == warm_rounds) {
+            // ---- end of warm-up: cooperative reduction of the staged keys (all consumer warps) ----
+            uint32_t tiles_w = warm_rounds * n_slots;
+            if (tiles_w > my_tiles) tiles_w = my_tiles;
+            const uint32_t n_keys = tiles_w * p.tile_rows;
+            const uint32_t n_chunks = (n_keys + kCandPerWarp - 1) / kCandPerWarp;
+            named_bar_sync(1, kConsumerWarps * 32);
+            coop_top128(cand_all, n_keys, n_chunks, warp, lane);
+            if (warp == 0) {
+                for (int i = lane; i < kCandPerWarp; i += 32) top[i] = cand_all[i];
+                __syncwarp();
+                if (lane == 0) *thr = top[p.k - 1];
+            }
+            named_bar_sync(1, kConsumerWarps * 32);
+            warm = false;
+        }
+        if (t >= my_tiles) {
+            if (warm) continue;  // (fewer tiles than warm-up rounds: keep counting rounds up to the barrier)
+            break;
+        }
         mbar_wait(&full[slot], parity);
-        const uint64_t tile = blockIdx.x + t * gridDim.x;
-        const uint64_t row0 = tile * p.tile_rows;
-        const uint32_t rows_valid = (uint32_t)((p.count - row0) < p.tile_rows ? (p.count - row0) : p.tile_rows);
-        const uint32_t *sl = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * p.slot_bytes);
+        const uint32_t row0 = (blockIdx.x + t * gridDim.x) * p.tile_rows;
+        const uint32_t left = p.count - row0;
+        const uint32_t rows_valid = left < p.tile_rows ? left : p.tile_rows;
+        const uint32_t rows_iter = warm ? p.tile_rows : rows_valid;  // warm-up also writes the empty keys of missing rows
 
-        for (uint32_t b = 0; b < rows_valid; b += kBatchRows) {
+        for (uint32_t b = member * kBatchRows; b < rows_iter; b += batch_stride) {
             uint32_t acc[kBatchRows];
 #pragma unroll
             for (int r = 0; r < kBatchRows; r++) acc[r] = 0;
-            const uint32_t *base = sl + (size_t)b * rw + p.hdr_words + lane;
+            const uint32_t *base = sl + b * rw + p.hdr_words + lane;
 #pragma unroll
             for (int j = 0; j < WPL; j++) {
-                if (jv[j]) {
+                if (FULL || jv[j]) {
 #pragma unroll
                     for (int r = 0; r < kBatchRows; r++) acc[r] = scan_op<OP>(base[r * rw + 32 * j], q[j], acc[r]);
                 }
             }
-            // butterfly: 16 rows x 32 lanes -> lane pair (2r, 2r+1) holds row r
+            // butterfly: 8 rows x 32 lanes -> the 4 lanes with (lane >> 2) pattern rr hold row rr
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                uint32_t keep = upper16 ? acc[i + 8] : acc[i], send = upper16 ? acc[i] : acc[i + 8];
+            for (int i = 0; i < 4; i++) {
+                uint32_t keep = upper16 ? acc[i + 4] : acc[i], send = upper16 ? acc[i] : acc[i + 4];
                 acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
             }
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                uint32_t keep = upper8 ? acc[i + 4] : acc[i], send = upper8 ? acc[i] : acc[i + 4];
+            for (int i = 0; i < 2; i++) {
+                uint32_t keep = upper8 ? acc[i + 2] : acc[i], send = upper8 ? acc[i] : acc[i + 2];
                 acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
             }
-#pragma unroll
-            for (int i = 0; i < 2; i++) {
-                uint32_t keep = upper4 ? acc[i + 2] : acc[i], send = upper4 ? acc[i] : acc[i + 2];
-                acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-            }
             {
-                uint32_t keep = upper2 ? acc[1] : acc[0], send = upper2 ? acc[0] : acc[1];
-                acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+                uint32_t keep = upper4 ? acc[1] : acc[0], send = upper4 ? acc[0] : acc[1];
+                acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
             }
+            acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 2);
             const uint32_t total = acc[0] + __shfl_xor_sync(0xffffffffu, acc[0], 1);
 
-            // epilogue: one row per even lane
+            // epilogue: one row per lane group of 4 (lane & 3 == 0 reports)
             const uint32_t rit = b + rr;
-            const bool valid = !(lane & 1) && rit < rows_valid;
+            const bool valid = !(lane & 3) && rit < rows_valid;
             float score;
             if (OP == kOpXor) {
                 // calculate_metric, encoded_vectors_binary.rs:237-252 (all values small integers, exact)
@@ -177,23 +222,27 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
                 score = p.bin_zx ? __fsub_rn(z, x) : __fsub_rn(x, z);
             } else {
                 // multiplier * S + query.offset + vector_offset, left to right, no FMA (u8.rs:347)
-                const float vo = __uint_as_float(sl[(size_t)rit * rw]);
+                const float vo = __uint_as_float(sl[rit * rw]);
                 score = __fadd_rn(__fadd_rn(__fmul_rn(p.multiplier, __uint2float_rn(total)), q_off), vo);
             }
-            const uint64_t grow = row0 + rit;
+            const uint32_t grow = row0 + rit;
             if (p.scores && valid) p.scores[grow] = score;
             if (do_topk) {
-                const uint64_t key = make_key(score, p.id_base + (uint32_t)grow, p.flip);
-                const bool pass = valid && key > *thr;
-                const uint32_t m = __ballot_sync(0xffffffffu, pass);
-                if (m) {
-                    const int n = __popc(m);
-                    if (cnt + n > kCandPerWarp) {
-                        cta_topk_flush(st, cand, cnt, lane);
-                        cnt = 0;
+                const uint64_t key = make_key(score, p.id_base + grow, p.flip);
+                if (warm) {
+                    if (!(lane & 3)) cand_all[t * p.tile_rows + rit] = valid ? key : 0ull;
+                } else {
+                    const bool pass = valid && key > *thr;
+                    const uint32_t m = __ballot_sync(0xffffffffu, pass);
+                    if (m) {
+                        const int n = __popc(m);
+                        if (cnt + n > kCandPerWarp) {
+                            cta_topk_flush(st, cand, cnt, lane);
+                            cnt = 0;
+                        }
+                        if (pass) cand[cnt + __popc(m & ((1u << lane) - 1))] = key;
+                        cnt += n;
                     }
-                    if (pass) cand[cnt + __popc(m & ((1u << lane) - 1))] = key;
-                    cnt += n;
                 }
             }
         }
@@ -203,7 +252,25 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
 
     if (do_topk) {
         __syncwarp();
-        if (cnt > 0) cta_topk_flush(st, cand, cnt, lane);
+        if (coop) {
+            // every warp pads its leftovers to a full chunk; the 16 chunks are reduced together
+            for (int i = cnt + lane; i < kCandPerWarp; i += 32) cand[i] = 0ull;
+            named_bar_sync(1, kConsumerWarps * 32);
+            coop_top128(cand_all, kConsumerWarps * kCandPerWarp, kConsumerWarps, warp, lane);
+            if (warp == 0) {
+                uint64_t t4[4];
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    const uint64_t a = top[lane * 4 + r], b = cand_all[kCandPerWarp - 1 - (lane * 4 + r)];
+                    t4[r] = a > b ? a : b;
+                }
+                reg128_merge_desc(t4, lane);
+#pragma unroll
+                for (int r = 0; r < 4; r++) top[lane * 4 + r] = t4[r];
+            }
+        } else if (cnt > 0) {
+            cta_topk_flush(st, cand, cnt, lane);
+        }
         named_bar_sync(1, kConsumerWarps * 32);
         uint64_t *out = p.partial + (size_t)blockIdx.x * p.Kp;
         for (uint32_t i = threadIdx.x; i < p.Kp; i += kConsumerWarps * 32) out[i] = top[i];

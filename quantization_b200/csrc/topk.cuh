@@ -68,8 +68,142 @@ struct CtaTopK {
     uint32_t k, Kp;
 };
 
+// ---------------------------------------------------------------------------------------------
+// Register-resident bitonic networks over 128 keys held 4 per lane ("blocked": element e lives in
+// lane e / 4, register e % 4).  Strides >= 4 exchange whole registers between lanes with
+// shuffles, strides 1 and 2 stay inside the lane.  No shared memory, no __syncwarp.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int mask) {
+    const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, mask);
+    const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), mask);
+    return ((uint64_t)hi << 32) | lo;
+}
+__device__ __forceinline__ uint64_t shfl_idx_u64(uint64_t v, int src) {
+    const uint32_t lo = __shfl_sync(0xffffffffu, (uint32_t)v, src);
+    const uint32_t hi = __shfl_sync(0xffffffffu, (uint32_t)(v >> 32), src);
+    return ((uint64_t)hi << 32) | lo;
+}
+__device__ __forceinline__ void ce_reg(uint64_t &a, uint64_t &b, bool desc) {  // a is the lower index
+    const bool swap = desc ? (a < b) : (a > b);
+    const uint64_t x = swap ? b : a, y = swap ? a : b;
+    a = x;
+    b = y;
+}
+// one (size, stride) step of the network; `desc_all` forces one direction (a merge step)
+template <bool MERGE_DESC>
+__device__ __forceinline__ void reg128_step(uint64_t (&v)[4], int size, int stride, int lane) {
+    if (stride >= 4) {
+        const int lm = stride >> 2;
+        const bool lower = (lane & lm) == 0;
+        const bool desc = MERGE_DESC || (((lane << 2) & size) == 0);
+        const bool keep_max = lower == desc;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint64_t o = shfl_xor_u64(v[r], lm);
+            v[r] = keep_max ? (v[r] > o ? v[r] : o) : (v[r] < o ? v[r] : o);
+        }
+    } else if (stride == 2) {
+        const bool desc = MERGE_DESC || (((lane << 2) & size) == 0);
+        ce_reg(v[0], v[2], desc);
+        ce_reg(v[1], v[3], desc);
+    } else {
+        // stride 1: elements (0,1) and (2,3); for size 2 the two pairs sort in opposite directions
+        const bool d0 = MERGE_DESC || ((((lane << 2) | 0) & size) == 0);
+        const bool d1 = MERGE_DESC || ((((lane << 2) | 2) & size) == 0);
+        ce_reg(v[0], v[1], d0);
+        ce_reg(v[2], v[3], d1);
+    }
+}
+// full sort, descending
+__device__ __forceinline__ void reg128_sort_desc(uint64_t (&v)[4], int lane) {
+#pragma unroll
+    for (int size = 2; size <= 128; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            if (size == 128) reg128_step<true>(v, size, stride, lane);
+            else reg128_step<false>(v, size, stride, lane);
+        }
+    }
+}
+// bitonic sequence -> sorted descending
+__device__ __forceinline__ void reg128_merge_desc(uint64_t (&v)[4], int lane) {
+#pragma unroll
+    for (int stride = 64; stride > 0; stride >>= 1) reg128_step<true>(v, 128, stride, lane);
+}
+
+// Cooperative reduction of n_chunks (<= 16) chunks of 128 keys in shared memory to the 128 largest,
+// sorted descending, in chunk 0.  Called by all kCoopWarps consumer warps (named barrier 1);
+// keys[n_keys .. n_chunks*128) is zero-filled here.  Chunk w is sorted by warp w in registers, then
+// a pairwise max-merge tree (log2(n_chunks) levels) runs with one warp per surviving pair.
+constexpr int kCoopWarps = 16;
+__device__ __forceinline__ void coop_top128(uint64_t *keys, uint32_t n_keys, uint32_t n_chunks, uint32_t warp,
+                                            uint32_t lane) {
+    for (uint32_t i = n_keys + warp * 32 + lane; i < n_chunks * 128; i += kCoopWarps * 32) keys[i] = 0ull;
+    asm volatile("bar.sync 1, %0;" ::"r"(kCoopWarps * 32) : "memory");
+    if (warp < n_chunks) {
+        uint64_t c[4];
+        uint64_t *ch = keys + warp * 128;
+#pragma unroll
+        for (int r = 0; r < 4; r++) c[r] = ch[lane * 4 + r];
+        reg128_sort_desc(c, (int)lane);
+#pragma unroll
+        for (int r = 0; r < 4; r++) ch[lane * 4 + r] = c[r];
+    }
+    for (uint32_t stride = 1; stride < n_chunks; stride <<= 1) {
+        asm volatile("bar.sync 1, %0;" ::"r"(kCoopWarps * 32) : "memory");
+        if ((warp & (2 * stride - 1)) == 0 && warp + stride < n_chunks) {
+            uint64_t *A = keys + warp * 128, *B = keys + (warp + stride) * 128;
+            uint64_t t[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const uint64_t a = A[lane * 4 + r], b = B[127 - (lane * 4 + r)];
+                t[r] = a > b ? a : b;
+            }
+            reg128_merge_desc(t, (int)lane);
+#pragma unroll
+            for (int r = 0; r < 4; r++) A[lane * 4 + r] = t[r];
+        }
+    }
+    asm volatile("bar.sync 1, %0;" ::"r"(kCoopWarps * 32) : "memory");
+}
+
 // Merge one warp's staged candidates cand[0..cnt) into the CTA list.  Called by a full warp.
 __device__ __forceinline__ void cta_topk_flush(const CtaTopK &st, uint64_t *cand, int cnt, int lane) {
+    if (st.Kp == (uint32_t)kCandPerWarp) {
+        // fast path (k <= 128): everything in registers; the lock covers ~12 network steps
+        uint64_t c[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) c[r] = (lane * 4 + r) < cnt ? cand[lane * 4 + r] : 0ull;
+        reg128_sort_desc(c, lane);
+        // reversed copy: element e <- element 127 - e  (lane 31 - lane, register 3 - r)
+        uint64_t rv[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) rv[r] = shfl_idx_u64(c[3 - r], 31 - lane);
+        if (lane == 0) {
+            while (atomicCAS(st.lock, 0, 1) != 0) {
+            }
+        }
+        __syncwarp();
+        __threadfence_block();
+        uint64_t t[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint64_t a = st.top[lane * 4 + r];
+            t[r] = a > rv[r] ? a : rv[r];  // top-128 of the union, as a bitonic sequence
+        }
+        reg128_merge_desc(t, lane);
+#pragma unroll
+        for (int r = 0; r < 4; r++) st.top[lane * 4 + r] = t[r];
+        const uint32_t ke = st.k - 1;
+        const uint32_t kr = ke & 3;
+        const uint64_t kth = kr == 0 ? t[0] : (kr == 1 ? t[1] : (kr == 2 ? t[2] : t[3]));
+        if ((uint32_t)lane == (ke >> 2)) *st.thr = kth;
+        __syncwarp();
+        __threadfence_block();
+        if (lane == 0) atomicExch(st.lock, 0);
+        __syncwarp();
+        return;
+    }
     for (int i = cnt + lane; i < kCandPerWarp; i += 32) cand[i] = 0;
     __syncwarp();
     warp_sort_desc(cand, kCandPerWarp, lane);
@@ -85,12 +219,8 @@ __device__ __forceinline__ void cta_topk_flush(const CtaTopK &st, uint64_t *cand
         tail[i] = a > b ? a : b;
     }
     __syncwarp();
-    if (st.Kp == (uint32_t)kCandPerWarp) {
-        warp_bitonic_merge<true>(st.top, kCandPerWarp, lane);
-    } else {
-        warp_bitonic_merge<false>(tail, kCandPerWarp, lane);  // tail ascending => [head desc | tail asc] is bitonic
-        warp_bitonic_merge<true>(st.top, (int)st.Kp, lane);
-    }
+    warp_bitonic_merge<false>(tail, kCandPerWarp, lane);  // tail ascending => [head desc | tail asc] is bitonic
+    warp_bitonic_merge<true>(st.top, (int)st.Kp, lane);
     if (lane == 0) *st.thr = st.top[st.k - 1];
     __syncwarp();
     __threadfence_block();
