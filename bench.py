@@ -50,6 +50,15 @@ def parse():
     return ap.parse_args()
 
 
+def ncu_traffic(workload):
+    """per-launch DRAM bytes of the dominant kernel from the committed ncu capture, or None"""
+    p = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    try:
+        return json.load(open(p)).get(workload, {}).get("bytes")
+    except Exception:
+        return None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -316,7 +325,8 @@ def run_gpu(args):
                     "d2h_bytes_per_step": int(enc.nbytes + k * 8), "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": {"u8": "row_scan_kernel<dot,12>", "bin": "row_scan_kernel<xor,2>",
+                         "traffic": ncu_traffic(args.workload) if rows == wl["rows"] else None,
+                         "kernel": {"u8": "row_scan_kernel<dot,12,full>", "bin": "row_scan_kernel<xor,2>",
                                                      "pq": "pq_scan_kernel"}[args.workload],
                          "kernel_ms": scan_ms, "kernel_launches_timed": kern_n, "peak_source": peak_src,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
