@@ -227,21 +227,17 @@ def run_gpu(args):
     q_host = host_query(wl)
     enc = ix.encode_query(q_host)                      # host blob through the C-ABI
     d_enc = torch.from_numpy(enc.copy()).to(dev)       # device-resident copy for the kernel-timed loop
-    d_keys = torch.zeros(k, dtype=torch.int64, device=dev)
-    d_all = torch.zeros(world * k, dtype=torch.int64, device=dev)
     d_scores = torch.zeros(k, dtype=torch.float32, device=dev)
     d_ids = torch.zeros(k, dtype=torch.int32, device=dev)
-    L = ctx._L
-    import ctypes as C
+    from quantization_b200.sharded import ShardedSearch
+    ss = ShardedSearch(ix, device=dev)  # scan -> all-gather of k keys per rank (NCCL) -> merge, on `stream`
 
     def step_dev():
+        nonlocal d_scores, d_ids
         if world == 1:
             ix.search_top_k_dev(d_enc.data_ptr(), k, True, 0, d_scores.data_ptr(), d_ids.data_ptr())
         else:
-            ix.search_top_k_dev(d_enc.data_ptr(), k, True, d_keys.data_ptr(), 0, 0)
-            dist.all_gather_into_tensor(d_all, d_keys)
-            ctx.check(L.qz_merge_topk_dev(ctx.handle, C.c_void_p(d_all.data_ptr()), world, k, 1, None,
-                                          C.c_void_p(d_scores.data_ptr()), C.c_void_p(d_ids.data_ptr())))
+            d_scores, d_ids = ss.search_top_k_dev(d_enc.data_ptr(), k, True)
 
     def barrier():
         if world > 1:

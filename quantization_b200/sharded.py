@@ -1,0 +1,105 @@
+"""Point-id sharding of an encoded corpus over the GPUs of one box.
+
+One process per GPU.  Rank g holds rows [floor(g*N/G), floor((g+1)*N/G)) of the SAME host storage
+(a byte-range slice, no re-encoding) with id_base = its first row, so point ids stay global.  The
+only exchange per query is the all-gather of each rank's k best u64 keys (8*k bytes per rank) over
+`torch.distributed` (NCCL on GPUs), followed by the G*k -> k merge on every rank.  Keys order
+(score, then lower id) identically everywhere, so the result does not depend on G.
+
+The scan and the merge are libqz_cuda calls (qz_scan_topk_dev / qz_merge_topk_dev); this module is
+the host plumbing around them: shard arithmetic, buffers, the collective.  The two device steps are
+injectable (`local_topk`, `merge`) so that the plumbing can be exercised with world_size > 1 on a
+CPU box over gloo (tests/test_sharded_gloo.py), where no CUDA device exists.
+"""
+import ctypes as C
+
+import numpy as np
+
+
+def shard_range(count, rank, world):
+    """rows [lo, hi) of rank `rank`: contiguous, sizes differ by at most 1, union = [0, count)"""
+    return (rank * count) // world, ((rank + 1) * count) // world
+
+
+def shard_storage(storage, row_bytes, count, rank, world):
+    """(byte slice of a flat EncodedStorage for this rank, rows in it, id_base)"""
+    lo, hi = shard_range(count, rank, world)
+    return storage[lo * row_bytes: hi * row_bytes], hi - lo, lo
+
+
+def f32_order_bits(u):
+    u = np.asarray(u, np.uint32)
+    return np.where(u & np.uint32(0x80000000), ~u, u | np.uint32(0x80000000)).astype(np.uint32)
+
+
+def keys_to_results(keys, largest):
+    """decode u64 keys (csrc/common.cuh make_key) into (scores f32, ids u32); empty slots (key 0) are dropped"""
+    keys = np.asarray(keys, np.uint64)
+    keys = keys[keys != 0]
+    o = (keys >> np.uint64(32)).astype(np.uint32)
+    if not largest:
+        o = ~o
+    u = np.where(o & np.uint32(0x80000000), o & np.uint32(0x7FFFFFFF), ~o).astype(np.uint32)
+    ids = (np.uint32(0xFFFFFFFF) - (keys & np.uint64(0xFFFFFFFF)).astype(np.uint32)).astype(np.uint32)
+    return u.view(np.float32), ids
+
+
+def results_to_keys(scores, ids, largest):
+    """inverse of keys_to_results (host-side packing, used by the tests)"""
+    o = f32_order_bits(np.ascontiguousarray(scores, np.float32).view(np.uint32))
+    if not largest:
+        o = ~o
+    return (o.astype(np.uint64) << np.uint64(32)) | (np.uint32(0xFFFFFFFF) - np.asarray(ids, np.uint32)).astype(np.uint64)
+
+
+class ShardedSearch:
+    """search_top_k over all ranks' shards; every rank returns the same (scores, ids)."""
+
+    def __init__(self, index=None, group=None, device=None, *, local_topk=None, merge=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.index = index
+        self.device = device if device is not None else torch.device("cpu")
+        self._local_topk = local_topk if local_topk is not None else self._gpu_local_topk
+        self._merge = merge if merge is not None else self._gpu_merge
+        self._bufs = {}
+
+    # ---- device steps (the product path) -----------------------------------------------------------
+    def _buffers(self, k):
+        if k not in self._bufs:
+            t = self.torch
+            self._bufs[k] = (t.zeros(k, dtype=t.int64, device=self.device),
+                             t.zeros(self.world * k, dtype=t.int64, device=self.device),
+                             t.zeros(k, dtype=t.float32, device=self.device),
+                             t.zeros(k, dtype=t.int32, device=self.device))
+        return self._bufs[k]
+
+    def _gpu_local_topk(self, d_query, k, largest, d_keys):
+        self.index.search_top_k_dev(d_query, k, largest, d_keys.data_ptr(), 0, 0)
+
+    def _gpu_merge(self, d_all, n_lists, k, largest, d_scores, d_ids):
+        ctx = self.index.ctx
+        ctx.check(ctx._L.qz_merge_topk_dev(ctx.handle, C.c_void_p(d_all.data_ptr()), n_lists, k, int(bool(largest)),
+                                           None, C.c_void_p(d_scores.data_ptr()), C.c_void_p(d_ids.data_ptr())))
+
+    # ---- the step ------------------------------------------------------------------------------------
+    def search_top_k_dev(self, d_query, k, largest=True):
+        """asynchronous on the current stream; returns device tensors (scores[k], ids[k]) valid on every rank"""
+        d_keys, d_all, d_scores, d_ids = self._buffers(k)
+        self._local_topk(d_query, k, largest, d_keys)
+        if self.world > 1:
+            self.dist.all_gather_into_tensor(d_all, d_keys, group=self.group)
+        else:
+            d_all.copy_(d_keys)
+        self._merge(d_all, self.world, k, largest, d_scores, d_ids)
+        return d_scores, d_ids
+
+    def search_top_k(self, d_query, k, largest=True, total_count=None):
+        s, i = self.search_top_k_dev(d_query, k, largest)
+        s, i = s.cpu().numpy(), i.cpu().numpy().view(np.uint32)
+        n = k if total_count is None else min(k, total_count)
+        return s[:n].copy(), i[:n].copy()

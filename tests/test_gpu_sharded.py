@@ -1,0 +1,67 @@
+"""Sharded search on the GPU: G shards of one corpus resident on one device (a 1-GPU box can still run the
+whole path: per-shard qz_scan_topk_dev, concatenated keys = what the all-gather delivers, qz_merge_topk_dev),
+compared with the single-shard oracle.  Multi-process NCCL runs are bench.py --gpus N."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import oracle as O
+import quantization_b200 as qz
+from quantization_b200 import sharded as S
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("G", [1, 2, 4, 8])
+@pytest.mark.parametrize("codec", ["u8", "bin"])
+def test_shards_on_one_device(ctx, G, codec):
+    count, dim, k = 20011, 256, 100
+    dev = torch.device("cuda", 0)
+    if codec == "u8":
+        data = O.uniform(42, count * dim).reshape(count, dim)
+        full = O.OracleU8.encode(data, O.DOT, False)
+        rb, q = full.stride, full.encode_query(O.uniform(43, dim))
+    else:
+        data = O.signs(42, count * dim).reshape(count, dim)
+        full = O.OracleBin.encode(data, O.DOT, False, 16)
+        rb, q = full.row_bytes, full.encode_query(O.signs(43, dim))
+    d_q = torch.from_numpy(q.copy()).to(dev)
+    d_all = torch.zeros(G * k, dtype=torch.int64, device=dev)
+    shards = []
+    for g in range(G):
+        sl, n, base = S.shard_storage(full.storage, rb, count, g, G)
+        vp = qz.VectorParameters(dim, n, qz.DistanceType.Dot, False)
+        ix = (qz.EncodedVectorsU8(ctx, sl.copy(), vp, full.alpha, full.offset, full.multiplier, id_base=base)
+              if codec == "u8" else qz.EncodedVectorsBin(ctx, sl.copy(), vp, id_base=base))
+        ix.search_top_k_dev(d_q.data_ptr(), k, True, d_all[g * k:].data_ptr(), 0, 0)
+        shards.append(ix)
+    d_s = torch.zeros(k, dtype=torch.float32, device=dev)
+    d_i = torch.zeros(k, dtype=torch.int32, device=dev)
+    ctx.check(ctx._L.qz_merge_topk_dev(ctx.handle, C.c_void_p(d_all.data_ptr()), G, k, 1, None,
+                                       C.c_void_p(d_s.data_ptr()), C.c_void_p(d_i.data_ptr())))
+    ctx.synchronize()
+    ws, wi = full.search(q, k, True)
+    assert np.array_equal(d_i.cpu().numpy().view(np.uint32), wi)
+    assert np.array_equal(d_s.cpu().numpy().view(np.uint32), ws.view(np.uint32))
+    # host decode of the gathered keys agrees with the device merge
+    keys = np.sort(d_all.cpu().numpy().view(np.uint64))[::-1][:k]
+    hs, hi = S.keys_to_results(keys, True)
+    assert np.array_equal(hi, wi)
+    for ix in shards:
+        ix.close()
+
+
+def test_sharded_search_class_world1(ctx):
+    count, dim, k = 5000, 128, 50
+    data = O.uniform(1, count * dim).reshape(count, dim)
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.L2, True)
+    ix = qz.EncodedVectorsU8.encode(data, qz.VecStorageBuilder(), vp, None, lambda: False, ctx=ctx)
+    o = O.OracleU8.encode(data, O.L2, True)
+    q = ix.encode_query(O.uniform(2, dim))
+    dev = torch.device("cuda", 0)
+    ss = S.ShardedSearch(ix, device=dev)
+    s, i = ss.search_top_k(torch.from_numpy(q.copy()).to(dev).data_ptr(), k, True, total_count=count)
+    ws, wi = o.search(q, k, True)
+    assert np.array_equal(i, wi) and np.array_equal(s.view(np.uint32), ws.view(np.uint32))
