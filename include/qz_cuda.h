@@ -113,6 +113,18 @@ QZ_API qz_status qz_u8_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t cou
                                   uint64_t n_sample, uint64_t seed, const volatile int32_t *stop, uint8_t *d_out,
                                   float *alpha, float *offset, float *multiplier);
 
+/* Batched multi-query search (BASELINE config 5): nq f32 queries [nq][dim] against every row, the k best
+ * per query.  One call = encode_query for each query (u8.rs:290-329), the nq x count x actual_dim integer
+ * contraction on the tensor cores (tcgen05 kind::i8, the same sums impl_score_dot_* returns per pair,
+ * cpp/avx2.c:31-69), the score map of u8.rs:347 and a per-query top-k with the library's ordering contract.
+ * Dot and L2 only (L1 is not a contraction).  Outputs are [nq][k] row-major; slots past `count` hold
+ * NaN / 0xFFFFFFFF.  Both variants return after the work has completed.  The first call builds a
+ * device-side copy of the codes with a 16-byte-aligned pitch (count * actual_dim bytes). */
+QZ_API qz_status qz_u8_search_batch(qz_index *index, const float *queries, uint32_t nq, uint32_t k, int32_t largest,
+                                    float *scores, uint32_t *ids);
+QZ_API qz_status qz_u8_search_batch_dev(qz_index *index, const float *d_queries, uint32_t nq, uint32_t k,
+                                        int32_t largest, float *d_scores, uint32_t *d_ids);
+
 /* ---- binary quantizer (EncodedVectorsBin, encoded_vectors_binary.rs) ------------------------- */
 
 /* bytes per row for BitsStoreType u8 (store_bytes = 1, binary.rs:99-116) or u128 (16, :152-159) */

@@ -111,6 +111,9 @@ void qz_index_destroy(qz_index *ix) {
         cudaSetDevice(ix->ctx->device);
         cudaStreamSynchronize(ix->ctx->stream);
         cudaFree(ix->d_storage);
+        cudaFree(ix->d_codes_soa);
+        cudaFree(ix->d_voff_soa);
+        cudaFree(ix->d_batch);
         pq_index_free(ix);
     }
     delete ix;

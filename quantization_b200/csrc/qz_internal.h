@@ -53,6 +53,11 @@ struct qz_index {
     // u8 (Metadata, encoded_vectors_u8.rs:24-31)
     uint32_t actual_dim = 0;
     float alpha = 0, offset = 0, multiplier = 0;
+    // batched tensor-core path (u8_batch.cu): SoA mirror + per-batch scratch, built lazily
+    uint8_t *d_codes_soa = nullptr;  // [count][actual_dim]
+    float *d_voff_soa = nullptr;     // [count]
+    uint8_t *d_batch = nullptr;      // scratch arena for one batch call
+    size_t batch_bytes = 0;
     // binary
     int store = 16;
     // pq (Metadata, encoded_vectors_pq.rs:39-44)

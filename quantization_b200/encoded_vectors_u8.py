@@ -82,6 +82,23 @@ class EncodedVectorsU8(DeviceIndex):
         self.alpha, self.offset, self.multiplier = np.float32(a.value), np.float32(o.value), np.float32(m.value)
         return self
 
+    # ---- batched multi-query search on the tensor cores (BASELINE config 5) ------------------------
+    def search_batch(self, queries, k, largest=True):
+        """f32 queries [nq, dim] -> (scores [nq, k], ids [nq, k]); per query identical to
+        search_top_k(encode_query(q), k, largest) (slots past `count`: NaN / 0xFFFFFFFF)"""
+        q = np.ascontiguousarray(queries, np.float32)
+        if q.ndim != 2 or q.shape[1] != self.vector_parameters.dim:
+            raise EncodingError("ArgumentsError", f"queries must be [nq, {self.vector_parameters.dim}]")
+        nq = q.shape[0]
+        scores = np.empty((nq, k), np.float32)
+        ids = np.empty((nq, k), np.uint32)
+        self.ctx.check(self._L.qz_u8_search_batch(self.handle, ptr(q), nq, k, int(bool(largest)), ptr(scores), ptr(ids)))
+        return scores, ids
+
+    def search_batch_dev(self, d_queries, nq, k, largest, d_scores, d_ids):
+        self.ctx.check(self._L.qz_u8_search_batch_dev(self.handle, C.c_void_p(d_queries), nq, k, int(bool(largest)),
+                                                      C.c_void_p(d_scores), C.c_void_p(d_ids)))
+
     @staticmethod
     def get_quantized_vector_size(vector_parameters):
         """u8.rs:252-255"""

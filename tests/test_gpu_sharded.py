@@ -53,8 +53,13 @@ def test_shards_on_one_device(ctx, G, codec):
         ix.close()
 
 
-def test_sharded_search_class_world1(ctx):
+def test_sharded_search_class_world1():
+    """ShardedSearch mixes torch ops (copy / all-gather) with library launches, so the library context
+    must run on torch's current stream (as bench.py does)."""
     count, dim, k = 5000, 128, 50
+    stream = torch.cuda.Stream(device=0)
+    torch.cuda.set_stream(stream)
+    ctx = qz.Context(0, stream=stream.cuda_stream)
     data = O.uniform(1, count * dim).reshape(count, dim)
     vp = qz.VectorParameters(dim, count, qz.DistanceType.L2, True)
     ix = qz.EncodedVectorsU8.encode(data, qz.VecStorageBuilder(), vp, None, lambda: False, ctx=ctx)
@@ -65,3 +70,5 @@ def test_sharded_search_class_world1(ctx):
     s, i = ss.search_top_k(torch.from_numpy(q.copy()).to(dev).data_ptr(), k, True, total_count=count)
     ws, wi = o.search(q, k, True)
     assert np.array_equal(i, wi) and np.array_equal(s.view(np.uint32), ws.view(np.uint32))
+    torch.cuda.set_stream(torch.cuda.default_stream(0))
+    ix.close()
