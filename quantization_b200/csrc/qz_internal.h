@@ -56,6 +56,7 @@ struct qz_index {
     // batched tensor-core path (u8_batch.cu): SoA mirror + per-batch scratch, built lazily
     uint8_t *d_codes_soa = nullptr;  // [count][actual_dim]
     float *d_voff_soa = nullptr;     // [count]
+    float voff_absmax = 0.0f;        // max |vector offset| (bound used by the batched fast filter)
     uint8_t *d_batch = nullptr;      // scratch arena for one batch call
     size_t batch_bytes = 0;
     // binary

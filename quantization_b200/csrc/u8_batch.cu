@@ -1,6 +1,7 @@
 // u8_batch.cu — batched multi-query u8 search: tcgen05 int8 contraction + fused threshold filter,
 // candidate compaction, and the C-ABI entry points qz_u8_search_batch[_dev].  See u8_batch.cuh.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -30,32 +31,76 @@ __global__ void __launch_bounds__(256) u8_split_rows_kernel(const uint8_t *aos, 
     }
 }
 
+// max |x| over n floats (non-negative floats order like their bit patterns); NaN offsets poison the bound to +inf
+__global__ void __launch_bounds__(256) absmax_kernel(const float *x, uint64_t n, uint32_t *out) {
+    uint32_t m = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t b = __float_as_uint(x[i]) & 0x7FFFFFFFu;
+        if (b > 0x7F800000u) b = 0x7F800000u;
+        m = b > m ? b : m;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint32_t v = __shfl_xor_sync(0xffffffffu, m, o);
+        m = v > m ? v : m;
+    }
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+
 // ---------------------------------------------------------------------------------------------
 // the contraction
 // ---------------------------------------------------------------------------------------------
-template <bool LARGEST>
+// Drain one epilogue warp's candidate queue: every lane appends its share to the per-query buffers, so the whole
+// warp pays one counter round trip per 32 candidates.
+__device__ __noinline__ void queue_flush(const U8BatchParams &p, const uint64_t *qkeys, const uint32_t *qq, uint32_t n,
+                                            uint32_t lane) {
+    __syncwarp();
+    for (uint32_t e = lane; e < n; e += 32) {
+        const uint32_t q = qq[e];
+        const uint32_t pos = atomicAdd(p.cnt + q, 1u);
+        if (pos < p.cap) p.cand[(size_t)q * p.cap + pos] = qkeys[e];
+        else *p.overflow = 1u;
+    }
+    __syncwarp();
+}
+
+// CL = CTAs per cluster.  The CL CTAs of a cluster work on CL consecutive query blocks against the SAME corpus
+// tile: each loads its own A block and 1/CL of the B block, multicast to all of them, which divides the
+// L2 -> SM traffic of B by CL (the kernel is L2-bandwidth bound without it).
+template <bool LARGEST, int CL>
 __global__ void __launch_bounds__(kBatchThreads, 1)
     u8_batch_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_v,
                     const U8BatchParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint8_t *stage_base = smem;                                             // [stages][A 16K | B 32K], 1024-aligned
-    float *voff_s = reinterpret_cast<float *>(smem + (size_t)kBatchStages * kStageBytes);  // [2][256]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(voff_s + 2 * kBatchN);
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);      // 1024-aligned, still "shared"
+    uint8_t *stage_base = smem;                                                       // [stages][A 16K | B 32K]
+    float *voff_s = reinterpret_cast<float *>(smem + (size_t)kBatchStages * kStageBytes);  // [kVoffBufs][256]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(voff_s + kVoffBufs * kBatchN);
     uint64_t *full = bars, *empty = bars + kBatchStages, *tfull = bars + 2 * kBatchStages, *tempty = tfull + 2;
-    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tempty + 2);
+    uint64_t *vfull = tempty + 2, *vempty = vfull + kVoffBufs;
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(vempty + kVoffBufs);
+    uint64_t *queue_base = reinterpret_cast<uint64_t *>(bars + 32);  // [8 warps][kQueueCap] keys, then query ids
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t n_tiles = p.n_qb * p.n_ct;
+    // work items: (corpus tile, group of CL query blocks); cluster c takes items c, c + n_clusters, ...
+    const uint32_t rank = CL > 1 ? cluster_ctarank() : 0u;
+    const uint32_t cluster_id = blockIdx.x / CL, n_clusters = gridDim.x / CL;
+    const uint32_t qgroups = p.n_qb / CL;  // n_qb is padded to a multiple of CL by the host
+    const uint32_t n_items = qgroups * p.n_ct;
+    constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kBatchStages; s++) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], 1);
+            mbar_init(&empty[s], CL);  // one tcgen05.commit arrival from every CTA of the cluster
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(&tfull[b], 1);
-            mbar_init(&tempty[b], 4);
+            mbar_init(&tempty[b], 8);
+        }
+        for (int b = 0; b < kVoffBufs; b++) {
+            mbar_init(&vfull[b], 1);
+            mbar_init(&vempty[b], 8);
         }
         fence_mbar_init();
     }
@@ -65,22 +110,35 @@ __global__ void __launch_bounds__(kBatchThreads, 1)
     }
     tc_fence_before();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();  // every CTA's barriers exist before any remote arrival or multicast write
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
 
     if (warp == 0) {
         // ---------------- TMA producer ----------------
         if (lane == 0) {
-            uint32_t stage = 0, round = 0;
-            for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                const uint32_t qb = t % p.n_qb, ct = t / p.n_qb;
+            uint32_t stage = 0, round = 0, it = 0;
+            for (uint32_t t = cluster_id; t < n_items; t += n_clusters, it++) {
+                const uint32_t qb = (t % qgroups) * CL + rank, ct = t / qgroups;
                 const int32_t q0 = (int32_t)(qb * kBatchM), r0 = (int32_t)(p.row_begin + ct * kBatchN);
+                {   // this tile's 256 vector offsets (1 KB; the array is padded) through their own small ring
+                    const uint32_t vb = it % kVoffBufs, vuse = it / kVoffBufs;
+                    if (vuse > 0) mbar_wait_bounded(&vempty[vb], (vuse - 1) & 1);
+                    mbar_arrive_expect_tx(&vfull[vb], kBatchN * 4);
+                    bulk_g2s(voff_s + vb * kBatchN, p.voff + r0, kBatchN * 4, &vfull[vb]);
+                }
                 for (uint32_t kc = 0; kc < p.k_chunks; kc++) {
-                    if (round > 0) mbar_wait_bounded(&empty[stage], (round - 1) & 1);
+                    if (round > 0) mbar_wait_bounded(&empty[stage], (round - 1) & 1);  // free in EVERY CTA of the cluster
                     uint8_t *a = stage_base + (size_t)stage * kStageBytes, *b = a + kStageA;
                     mbar_arrive_expect_tx(&full[stage], kStageBytes);
                     tma_load_2d(a, &map_q, (int32_t)(kc * kBatchKC), q0, &full[stage]);
-                    tma_load_2d(b, &map_v, (int32_t)(kc * kBatchKC), r0, &full[stage]);
+                    if (CL == 1) {
+                        tma_load_2d(b, &map_v, (int32_t)(kc * kBatchKC), r0, &full[stage]);
+                    } else {  // this CTA's 1/CL of the rows, delivered to all CL CTAs
+                        constexpr uint32_t part = kBatchN / CL;
+                        tma_load_2d_mc(b + (size_t)rank * part * kBatchKC, &map_v, (int32_t)(kc * kBatchKC),
+                                       r0 + (int32_t)(rank * part), &full[stage], kMask);
+                    }
                     if (++stage == kBatchStages) {
                         stage = 0;
                         round++;
@@ -93,7 +151,7 @@ __global__ void __launch_bounds__(kBatchThreads, 1)
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_u8(kBatchM, kBatchN);
             uint32_t stage = 0, round = 0, it = 0;
-            for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x, it++) {
+            for (uint32_t t = cluster_id; t < n_items; t += n_clusters, it++) {
                 const uint32_t buf = it & 1, use = it >> 1;  // use = how many times this buffer was filled before
                 if (use > 0) mbar_wait_bounded(&tempty[buf], (use - 1) & 1);
                 tc_fence_after();
@@ -106,7 +164,9 @@ __global__ void __launch_bounds__(kBatchThreads, 1)
 #pragma unroll
                     for (uint32_t k4 = 0; k4 < kBatchKC / 32; k4++)  // K = 32 bytes per instruction: +32 B => +2 in the address field
                         umma_i8(d_tmem, ad + 2 * k4, bd + 2 * k4, idesc, (kc | k4) != 0);
-                    umma_commit(&empty[stage]);  // arrives when the MMAs above have read this stage
+                    // arrives (in every CTA of the cluster) when the MMAs above have read this stage
+                    if (CL == 1) umma_commit(&empty[stage]);
+                    else umma_commit_mc(&empty[stage], kMask);
                     if (++stage == kBatchStages) {
                         stage = 0;
                         round++;
@@ -116,69 +176,128 @@ __global__ void __launch_bounds__(kBatchThreads, 1)
             }
         }
     } else {
-        // ---------------- epilogue: thread = TMEM lane = one query of the block ----------------
-        const uint32_t quarter = warp & 3;  // warps 2,3,4,5 -> lane quarters 2,3,0,1
+        // ---------------- epilogue: thread = TMEM lane = one query; two warps per lane quarter ----------------
+        // warps 2..5 take columns [0,128), warps 6..9 columns [128,256) of the accumulator buffer.
+        const uint32_t quarter = warp & 3;  // warps 2,3,4,5 / 6,7,8,9 -> lane quarters 2,3,0,1
+        const uint32_t half = (warp - 2) >> 2;
         const uint32_t m = quarter * 32 + lane;
-        const uint32_t et = threadIdx.x - 64;  // 0..127 among the epilogue threads
+        const float kmax = fabsf(p.multiplier) * 16129.0f * (float)(p.k_chunks * kBatchKC);  // |multiplier * S| bound
+        uint64_t *qkeys = queue_base + (size_t)(warp - 2) * kQueueCap;                       // this warp's candidate queue
+        uint32_t *qq = reinterpret_cast<uint32_t *>(queue_base + 8 * kQueueCap) + (size_t)(warp - 2) * kQueueCap;
+        uint32_t qcount = 0;
         uint32_t it = 0;
-        for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x, it++) {
-            const uint32_t qb = t % p.n_qb, ct = t / p.n_qb;
+        // per-query state of the NEXT tile is fetched while the current one is processed
+        uint64_t thr_next = ~0ull;
+        float qo_next = 0.0f;
+        if (cluster_id < n_items) {
+            const uint32_t q = ((cluster_id % qgroups) * CL + rank) * kBatchM + m;
+            if (q < p.nq) {
+                thr_next = __ldcg(p.thr + q);
+                qo_next = __ldg(p.qoff + q);
+            }
+        }
+        for (uint32_t t = cluster_id; t < n_items; t += n_clusters, it++) {
+            const uint32_t qb = (t % qgroups) * CL + rank, ct = t / qgroups;
             const uint32_t buf = it & 1, use = it >> 1;
             const uint32_t q = qb * kBatchM + m;
             const bool q_ok = q < p.nq;
             const uint32_t r0 = p.row_begin + ct * kBatchN;
             const uint32_t n_valid = p.row_end - r0 < (uint32_t)kBatchN ? p.row_end - r0 : (uint32_t)kBatchN;
-            // stage this tile's vector offsets (shared by all queries)
-            float *vo = voff_s + buf * kBatchN;
-            for (uint32_t i = et; i < (uint32_t)kBatchN; i += 128) vo[i] = i < n_valid ? __ldg(p.voff + r0 + i) : 0.0f;
-            const uint64_t thr_key = q_ok ? __ldcg(p.thr + q) : ~0ull;
-            const float qo = q_ok ? __ldg(p.qoff + q) : 0.0f;
+            const uint32_t vb = it % kVoffBufs, vuse = it / kVoffBufs;
+            const float *vo = voff_s + vb * kBatchN;
+            const uint64_t thr_key = thr_next;
+            const float qo = qo_next;
+            {
+                const uint32_t tn = t + n_clusters;
+                thr_next = ~0ull;
+                qo_next = 0.0f;
+                if (tn < n_items) {
+                    const uint32_t qn = ((tn % qgroups) * CL + rank) * kBatchM + m;
+                    if (qn < p.nq) {
+                        thr_next = __ldcg(p.thr + qn);
+                        qo_next = __ldg(p.qoff + qn);
+                    }
+                }
+            }
             // score part of the threshold key; key 0 decodes to NaN so that everything passes
             const float thr_f = __uint_as_float(f32_from_order_bits((uint32_t)(thr_key >> 32) ^ p.flip));
-            named_bar_sync(1, 128);
+            // Fast filter: one FMA per element against a threshold loosened by far more than the rounding
+            // difference between fma(m, S, vo) + qo and the reference's three roundings (each <= 2^-24 of the
+            // magnitudes involved; the margin is 2^-20 of their sum).  Survivors are re-scored exactly below.
+            const float margin = (kmax + fabsf(qo) + p.voff_absmax + fabsf(thr_f)) * 9.5367431640625e-7f;
+            const float thr2 = LARGEST ? (thr_f - qo) - margin : (thr_f - qo) + margin;
+            mbar_wait_bounded(&vfull[vb], vuse & 1);
             mbar_wait_bounded(&tfull[buf], use & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + buf * kBatchN + ((quarter * 32) << 16);
-            for (uint32_t c = 0; c < (uint32_t)kBatchN / 32; c++) {
-                uint32_t r[32];
-                tmem_ld32(taddr + c * 32, r);
-                if (c * 32 >= n_valid) continue;  // (uniform) nothing valid in this column group
-                uint32_t pass = 0;
-                float sc[32];
+            const uint32_t taddr = tmem_base + buf * kBatchN + half * (kBatchN / 2) + ((quarter * 32) << 16);
+            uint32_t ra[32], rb[32];
+            tmem_ld32_nowait(taddr, ra);
+#pragma unroll
+            for (uint32_t c = 0; c < (uint32_t)kBatchN / 64; c++) {
+                // software pipeline: the load of group c+1 is in flight while group c is filtered
+                uint32_t(&r)[32] = (c & 1) ? rb : ra;
+                tmem_ld_wait(r);
+                if (c + 1 < (uint32_t)kBatchN / 64) {
+                    tmem_ld32_nowait(taddr + (c + 1) * 32, (c & 1) ? ra : rb);
+                    if (p.dbg & 1) tmem_ld_wait((c & 1) ? ra : rb);
+                }
+                if (p.dbg & 4) continue;
+                const uint32_t col0 = half * (kBatchN / 2) + c * 32;
+                if (col0 >= n_valid) continue;  // (uniform) nothing valid in this column group
+                const uint32_t left = n_valid - col0;
+                // fast filter: bit j of `mask` = column j may beat this lane's threshold
+                uint32_t mask = 0;
 #pragma unroll
                 for (int j = 0; j < 32; j++) {
-                    // multiplier * S + query.offset + vector_offset, left to right, no FMA (u8.rs:347)
-                    const float s = __fadd_rn(__fadd_rn(__fmul_rn(p.multiplier, __int2float_rn((int)r[j])), qo), vo[c * 32 + j]);
-                    sc[j] = s;
-                    const bool ok = LARGEST ? !(s < thr_f) : !(s > thr_f);
-                    pass |= ok ? (1u << j) : 0u;
+                    const float x = fmaf(p.multiplier, __int2float_rn((int)r[j]), vo[col0 + j]);
+                    const bool ok = LARGEST ? !(x < thr2) : !(x > thr2);
+                    mask |= ok ? (1u << j) : 0u;
                 }
-                if (!q_ok) pass = 0;
-                const uint32_t left = n_valid - c * 32;
-                if (left < 32) pass &= (1u << left) - 1;
-                while (pass) {
-                    const int j = __ffs(pass) - 1;
-                    pass &= pass - 1;
-                    float s = sc[0];
-#pragma unroll
-                    for (int jj = 1; jj < 32; jj++) s = (j == jj) ? sc[jj] : s;
-                    const uint64_t key = make_key(s, p.id_base + r0 + c * 32 + j, p.flip);
-                    if (key > thr_key) {
-                        const uint32_t pos = atomicAdd(p.cnt + q, 1u);
-                        if (pos < p.cap) p.cand[(size_t)q * p.cap + pos] = key;
-                        else *p.overflow = 1u;
+                if (!q_ok || (p.dbg & 2)) mask = 0;
+                if (left < 32) mask &= (1u << left) - 1;
+                // columns flagged by any lane are re-scored exactly by the whole warp (uniform control flow);
+                // the survivors go to the warp's shared-memory queue, one ballot per column
+                const uint32_t cols = __reduce_or_sync(0xffffffffu, mask);
+                uint32_t todo = cols;
+                while (todo) {  // rolled on purpose: the body exists once per column group (instruction cache)
+                    const uint32_t j = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const int S = (int)tmem_ld1(taddr + c * 32 + j);  // this lane's accumulator of column j again
+                    const float v = vo[col0 + j];
+                    // multiplier * S + query.offset + vector_offset, left to right, no FMA (u8.rs:347)
+                    const float sx = __fadd_rn(__fadd_rn(__fmul_rn(p.multiplier, __int2float_rn(S)), qo), v);
+                    const uint64_t key = make_key(sx, p.id_base + r0 + col0 + j, p.flip);
+                    const bool ok = ((mask >> j) & 1u) && key > thr_key;
+                    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+                    if (bal) {
+                        if (qcount + 32 > (uint32_t)kQueueCap) {
+                            queue_flush(p, qkeys, qq, qcount, lane);
+                            qcount = 0;
+                        }
+                        if (ok) {
+                            const uint32_t w = qcount + __popc(bal & ((1u << lane) - 1));
+                            qkeys[w] = key;
+                            qq[w] = q;
+                        }
+                        qcount += __popc(bal);
                     }
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[buf]);
+            if (lane == 0) {
+                mbar_arrive(&tempty[buf]);
+                mbar_arrive(&vempty[vb]);
+            }
         }
+        queue_flush(p, qkeys, qq, qcount, lane);
     }
 
     tc_fence_before();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();  // no CTA leaves while a peer may still write its shared memory or barriers
     if (warp == 1) {
+        __syncwarp();
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
     }
@@ -286,10 +405,18 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
     // ---- SoA mirror of the corpus (once) ----
     if (!ix->d_codes_soa && N) {
         QZ_CUDA(ctx, cudaMalloc((void **)&ix->d_codes_soa, align_up((size_t)N * K, 256)));
-        QZ_CUDA(ctx, cudaMalloc((void **)&ix->d_voff_soa, align_up((size_t)N * 4, 256)));
+        // (+2 KB: the kernel always stages whole 256-row blocks of offsets; the last 4 bytes hold max |offset|)
+        const size_t vb = align_up((size_t)N * 4, 256) + 2048;
+        QZ_CUDA(ctx, cudaMalloc((void **)&ix->d_voff_soa, vb));
+        QZ_CUDA(ctx, cudaMemsetAsync(ix->d_voff_soa, 0, vb, ctx->stream));
         u8_split_rows_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ix->d_storage, N, K, ix->d_codes_soa, ix->d_voff_soa);
         QZ_CUDA(ctx, cudaGetLastError());
-        ctx->launches++;
+        uint32_t *d_amax = reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(ix->d_voff_soa) + vb - 4);
+        absmax_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(ix->d_voff_soa, N, d_amax);
+        QZ_CUDA(ctx, cudaGetLastError());
+        QZ_CUDA(ctx, cudaMemcpyAsync(&ix->voff_absmax, d_amax, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->launches += 2;
     }
     // ---- scratch arena ----
     const uint32_t cap = k <= 256 ? 4096u : 8192u;
@@ -316,24 +443,63 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
     QZ_CUDA(ctx, cudaGetLastError());
     ctx->launches++;
 
-    static bool attr_done = false;
-    if (!attr_done) {
-        QZ_CUDA(ctx, cudaFuncSetAttribute(u8_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBatchSmem));
-        QZ_CUDA(ctx, cudaFuncSetAttribute(u8_batch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBatchSmem));
+    // ---- cluster size: 4, 2 or 1 CTAs share each corpus tile (QZ_BATCH_CLUSTER overrides) ----
+    static int cl_pick = 0, cl_grid[5] = {0, 0, 0, 0, 0};
+    if (!cl_pick) {
+        const void *fns[5][2] = {{nullptr, nullptr},
+                                 {(const void *)u8_batch_kernel<true, 1>, (const void *)u8_batch_kernel<false, 1>},
+                                 {(const void *)u8_batch_kernel<true, 2>, (const void *)u8_batch_kernel<false, 2>},
+                                 {nullptr, nullptr},
+                                 {(const void *)u8_batch_kernel<true, 4>, (const void *)u8_batch_kernel<false, 4>}};
+        for (int cl : {1, 2, 4}) {
+            for (int j = 0; j < 2; j++)
+                QZ_CUDA(ctx, cudaFuncSetAttribute(fns[cl][j], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBatchSmem));
+            if (cl == 1) {
+                cl_grid[1] = ctx->sm_count;
+                continue;
+            }
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(ctx->sm_count / cl * cl);
+            cfg.blockDim = dim3(kBatchThreads);
+            cfg.dynamicSmemBytes = kBatchSmem;
+            cudaLaunchAttribute at;
+            at.id = cudaLaunchAttributeClusterDimension;
+            at.val.clusterDim.x = cl;
+            at.val.clusterDim.y = at.val.clusterDim.z = 1;
+            cfg.attrs = &at;
+            cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, fns[cl][0], &cfg) != cudaSuccess) {
+                cudaGetLastError();
+                n = 0;
+            }
+            if (n > ctx->sm_count / cl) n = ctx->sm_count / cl;
+            cl_grid[cl] = n * cl;
+        }
         QZ_CUDA(ctx, cudaFuncSetAttribute(u8_batch_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
-        attr_done = true;
+        // widest cluster that keeps at least ~95% of the SMs busy
+        cl_pick = 1;
+        for (int cl : {2, 4})
+            if (cl_grid[cl] * 100 >= ctx->sm_count * 95) cl_pick = cl;
+        if (const char *e = getenv("QZ_BATCH_CLUSTER")) {
+            const int v = atoi(e);
+            if ((v == 1 || v == 2 || v == 4) && cl_grid[v] > 0) cl_pick = v;
+        }
     }
+    const int CL = cl_pick;
     CUtensorMap map_q, map_v;
-    if (!make_map(&map_q, d_qcodes, nq, K, kBatchM) || (N && !make_map(&map_v, ix->d_codes_soa, N, K, kBatchN)))
+    if (!make_map(&map_q, d_qcodes, nq, K, kBatchM) || (N && !make_map(&map_v, ix->d_codes_soa, N, K, kBatchN / CL)))
         return fail(ctx, QZ_ENCODING, "cuTensorMapEncodeTiled failed");
     if (!N) memset(&map_v, 0, sizeof map_v);
 
     U8BatchParams p{};
     p.nq = nq;
     p.k_chunks = (K + kBatchKC - 1) / kBatchKC;
-    p.n_qb = (nq + kBatchM - 1) / kBatchM;
+    p.n_qb = ((nq + kBatchM - 1) / kBatchM + CL - 1) / CL * CL;  // padded: whole groups of CL query blocks
     p.qoff = d_qoff;
     p.voff = ix->d_voff_soa;
+    p.voff_absmax = ix->voff_absmax;
+    p.dbg = getenv("QZ_BATCH_DBG") ? (uint32_t)atoi(getenv("QZ_BATCH_DBG")) : 0u;
     p.multiplier = ix->multiplier;
     p.id_base = ix->id_base;
     p.flip = largest ? 0u : 0xFFFFFFFFu;
@@ -351,7 +517,9 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
     for (int safe = 0; safe < 2; safe++) {
         QZ_CUDA(ctx, cudaMemsetAsync(a + o_thr, 0, o_cand - o_thr, ctx->stream));  // thr, cnt, overflow
         uint64_t done = 0;
-        const uint64_t first = (cap - (safe ? k : 0)) / kBatchN * kBatchN ? (cap - (safe ? k : 0)) / kBatchN * kBatchN : kBatchN;
+        // (fast schedule: the first chunk is only cap/4 rows: all of them become candidates, and the first
+        // compaction sorts that many keys per query)
+        const uint64_t first = safe ? ((cap - k) / kBatchN * kBatchN ? (cap - k) / kBatchN * kBatchN : kBatchN) : cap / 4;
         do {
             uint64_t R = first;
             if (!safe && done) {
@@ -365,13 +533,30 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
                 p.row_begin = (uint32_t)done;
                 p.row_end = (uint32_t)(done + R);
                 p.n_ct = (uint32_t)((R + kBatchN - 1) / kBatchN);
-                const uint32_t tiles = p.n_qb * p.n_ct;
-                const uint32_t grid = tiles < (uint32_t)ctx->sm_count ? tiles : (uint32_t)ctx->sm_count;
+                const uint32_t items = p.n_qb / CL * p.n_ct;
+                const uint32_t max_clusters = (uint32_t)cl_grid[CL] / CL;
+                const uint32_t grid = (items < max_clusters ? items : max_clusters) * CL;
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3(grid);
+                cfg.blockDim = dim3(kBatchThreads);
+                cfg.dynamicSmemBytes = kBatchSmem;
+                cfg.stream = ctx->stream;
+                cudaLaunchAttribute at;
+                at.id = cudaLaunchAttributeClusterDimension;
+                at.val.clusterDim.x = CL;
+                at.val.clusterDim.y = at.val.clusterDim.z = 1;
+                cfg.attrs = &at;
+                cfg.numAttrs = 1;
+                cudaError_t le;
                 timing_begin(ctx);
-                if (largest) u8_batch_kernel<true><<<grid, kBatchThreads, kBatchSmem, ctx->stream>>>(map_q, map_v, p);
-                else u8_batch_kernel<false><<<grid, kBatchThreads, kBatchSmem, ctx->stream>>>(map_q, map_v, p);
+                if (CL == 4) le = largest ? cudaLaunchKernelEx(&cfg, u8_batch_kernel<true, 4>, map_q, map_v, p)
+                                          : cudaLaunchKernelEx(&cfg, u8_batch_kernel<false, 4>, map_q, map_v, p);
+                else if (CL == 2) le = largest ? cudaLaunchKernelEx(&cfg, u8_batch_kernel<true, 2>, map_q, map_v, p)
+                                               : cudaLaunchKernelEx(&cfg, u8_batch_kernel<false, 2>, map_q, map_v, p);
+                else le = largest ? cudaLaunchKernelEx(&cfg, u8_batch_kernel<true, 1>, map_q, map_v, p)
+                                  : cudaLaunchKernelEx(&cfg, u8_batch_kernel<false, 1>, map_q, map_v, p);
                 timing_end(ctx);
-                QZ_CUDA(ctx, cudaGetLastError());
+                QZ_CUDA(ctx, le);
                 ctx->launches++;
             }
             cp.final_out = last;

@@ -10,7 +10,7 @@
 //               128-query x 128-byte A block and a 256-row x 128-byte B block per pipeline stage
 //   warp 1      MMA issuer: tcgen05.mma.cta_group::1.kind::i8, u8 x u8 -> s32, M=128 N=256 K=32 per
 //               instruction, accumulators in TMEM (2 buffers x 256 columns), tcgen05.commit frees stages
-//   warps 2..5  epilogue: tcgen05.ld (thread = TMEM lane = one query), affine map, threshold filter
+//   warps 2..9  epilogue: tcgen05.ld (thread = TMEM lane = one query), affine map, threshold filter
 //               against the query's current k-th best key, survivors appended to the query's
 //               candidate buffer in global memory
 // Operands come from a device-side SoA mirror (codes[N][K] contiguous, offsets[N]) because the
@@ -26,11 +26,13 @@ constexpr int kBatchM = 128;       // queries per tile (TMEM lanes)
 constexpr int kBatchN = 256;       // corpus rows per tile (TMEM columns per accumulator buffer)
 constexpr int kBatchKC = 128;      // code bytes per pipeline stage = one 128-byte swizzle row
 constexpr int kBatchStages = 4;
-constexpr int kBatchThreads = 192;  // producer, MMA, 4 epilogue warps
+constexpr int kQueueCap = 256;     // candidates an epilogue warp can stage in shared memory between flushes
+constexpr int kVoffBufs = 4;       // ring of per-tile vector-offset blocks (1 KB each)
+constexpr int kBatchThreads = 320;  // producer, MMA, 8 epilogue warps
 constexpr uint32_t kStageA = kBatchM * kBatchKC;  // 16 KB
 constexpr uint32_t kStageB = kBatchN * kBatchKC;  // 32 KB
 constexpr uint32_t kStageBytes = kStageA + kStageB;
-constexpr size_t kBatchSmem = (size_t)kBatchStages * kStageBytes + 2 * kBatchN * 4 + 256 + 1024;  // + voff x2, barriers, align slack
+constexpr size_t kBatchSmem = (size_t)kBatchStages * kStageBytes + kVoffBufs * kBatchN * 4 + 256 + 1024 + 8 * kQueueCap * 12;  // + voff ring, barriers, align slack, queues, barriers, align slack
 
 struct U8BatchParams {
     uint32_t nq, k_chunks;       // queries; ceil(actual_dim / 128)
@@ -38,12 +40,13 @@ struct U8BatchParams {
     uint32_t n_qb, n_ct;         // query blocks, corpus tiles in the chunk
     const float *qoff;           // [nq]
     const float *voff;           // [count]
-    float multiplier;
+    float multiplier, voff_absmax;  // voff_absmax = max |vector offset| over the index
     uint32_t id_base, flip, cap;
     const uint64_t *thr;         // [nq] current k-th best key (0 = none yet)
     uint64_t *cand;              // [nq][cap]
     uint32_t *cnt;               // [nq]
     uint32_t *overflow;          // set when a candidate did not fit
+    uint32_t dbg;                // experiment switches (0 in production)
 };
 
 // bounded spin: a pipeline bug traps (launch failure) instead of hanging the device
@@ -88,6 +91,31 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
 }
+// multicast forms for thread-block clusters: the B block of a stage is loaded once from L2 and delivered to the
+// same shared-memory offset of every CTA in `mask`; a stage is released in every CTA of the cluster
+__device__ __forceinline__ void tma_load_2d_mc(void *dst, const CUtensorMap *map, int32_t c0, int32_t c1, uint64_t *bar,
+                                               uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, "
+        "%4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint64_t *bar, uint16_t mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"(mask)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -102,6 +130,34 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr));
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+// one accumulator (this lane's row, one column); waits for every outstanding tcgen05.ld of the thread
+__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
+    uint32_t v;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\ttcgen05.wait::ld.sync.aligned;" : "=r"(v) : "r"(taddr) : "memory");
+    return v;
+}
+// the registers are tied to the wait so that no use of them can be scheduled above it
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                   "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]),
+                   "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]),
+                   "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :
+                 : "memory");
 }
 
 }  // namespace qz
