@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — scored vectors/s of the encoded-vector scan on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload u8|bin|pq] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload u8|bin|pq|u8batch] [--impl reference]
 
 A step = one full scan of the rank's shard against one encoded query, fused top-k included, plus
 (N > 1) the all-gather of the per-rank top-k keys over NCCL and the final merge.  Weak scaling:
@@ -33,6 +33,10 @@ WORKLOADS = {
                 name="EncodedVectorsBin xor-popcount scan, 10M x 1536-bit, top-100 (BASELINE config 3)"),
     "pq": dict(rows=1_000_000, dim=1536, row_bytes=768, k=100, dtype="f32",
                name="EncodedVectorsPQ LUT scan, 1M x 1536-d, chunk 2 (768 codes/vector), top-100 (BASELINE config 4)"),
+    # BASELINE config 5 per GPU: 4096 queries x 1.25M rows x 768-d on the tensor cores (rows = 10M / 8 GPUs)
+    "u8batch": dict(rows=1_250_000, dim=768, row_bytes=772, k=100, dtype="u8", nq=4096,
+                    name="batched EncodedVectorsU8 dot search, 4096 queries x 1.25M rows per GPU x 768-d, top-100 "
+                         "per query, tcgen05 int8 (BASELINE config 5, 10M rows over 8 GPUs)"),
 }
 METRIC = "scored vectors/s (u8 dot, 1M x 1536)"
 
@@ -40,14 +44,17 @@ METRIC = "scored vectors/s (u8 dot, 1M x 1536)"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=1000)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=0, help="default 1000 (20 for u8batch)")
+    ap.add_argument("--warmup", type=int, default=0, help="default 20 (3 for u8batch)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="u8", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the workload's BASELINE size)")
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="rows of the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    a.steps = a.steps or (20 if a.workload == "u8batch" else 1000)
+    a.warmup = a.warmup or (3 if a.workload == "u8batch" else 20)
+    return a
 
 
 def ncu_traffic(workload):
@@ -337,6 +344,168 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------ batched arm
+def run_gpu_batch(args):
+    """BASELINE config 5: a step = one batched search (encode nq queries, int8 contraction on the tensor cores,
+    per-query top-k) over the rank's shard, + for N > 1 the all-gather of the [nq][k] results and the
+    per-query merge.  value = nq * rows * N / t (scored (query, vector) pairs per second)."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    import quantization_b200 as qz
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    wl = WORKLOADS["u8batch"]
+    rows, dim, k, nq = args.rows or wl["rows"], wl["dim"], wl["k"], wl["nq"]
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ctx = qz.Context(local, stream=stream.cuda_stream)
+    g = torch.Generator(device=dev)
+    g.manual_seed(42 + rank)
+    data = torch.rand((rows, dim), generator=g, device=dev, dtype=torch.float32)
+    ix = qz.EncodedVectorsU8.encode_dev(data.data_ptr(), qz.VectorParameters(dim, rows, qz.DistanceType.Dot, False), None,
+                                        ctx=ctx, id_base=rank * rows)
+    del data
+    q_host = np.random.default_rng(43).random((nq, dim), dtype=np.float32)
+    q_pin = torch.from_numpy(q_host).pin_memory()
+    d_q = q_pin.to(dev)
+    d_s = torch.zeros((nq, k), dtype=torch.float32, device=dev)
+    d_i = torch.zeros((nq, k), dtype=torch.int32, device=dev)
+    d_as = torch.zeros((world, nq, k), dtype=torch.float32, device=dev)
+    d_ai = torch.zeros((world, nq, k), dtype=torch.int32, device=dev)
+    d_ms = torch.zeros((nq, k), dtype=torch.float32, device=dev)
+    d_mi = torch.zeros((nq, k), dtype=torch.int32, device=dev)
+    L = ctx._L
+
+    def step_dev(dq):
+        ix.search_batch_dev(dq.data_ptr(), nq, k, True, d_s.data_ptr(), d_i.data_ptr())
+        if world > 1:
+            dist.all_gather_into_tensor(d_as, d_s)
+            dist.all_gather_into_tensor(d_ai, d_i)
+            ctx.check(L.qz_merge_topk_batch_dev(ctx.handle, C.c_void_p(d_as.data_ptr()), C.c_void_p(d_ai.data_ptr()), world,
+                                                nq, k, 1, C.c_void_p(d_ms.data_ptr()), C.c_void_p(d_mi.data_ptr())))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step_dev(d_q)
+    barrier()
+    if rank == 0:
+        sampler.lines.clear()
+    launches0 = ctx.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_dev(d_q)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ctx.launch_count - launches0
+    ctx.set_timing(True)
+    for _ in range(args.steps):
+        step_dev(d_q)
+    barrier()
+    kern_ms, kern_n = ctx.get_timing()
+    ctx.set_timing(False)
+    clocks = sampler.stop() if rank == 0 else None
+    # e2e: pinned host queries -> H2D -> search -> D2H of the [nq][k] results, every step
+    h_s = torch.empty((nq, k), dtype=torch.float32).pin_memory()
+    h_i = torch.empty((nq, k), dtype=torch.int32).pin_memory()
+    d_q2 = torch.empty_like(d_q)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        d_q2.copy_(q_pin, non_blocking=True)
+        step_dev(d_q2)
+        h_s.copy_(d_ms if world > 1 else d_s, non_blocking=True)
+        h_i.copy_(d_mi if world > 1 else d_i, non_blocking=True)
+        torch.cuda.synchronize()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    tm = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(tm[0]), float(tm[1])
+    if rank == 0:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+            os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        bf16 = float(pk.get("bf16_tflops", 1590.0))
+        peak = 2.0 * bf16  # no measured int8 figure exists: the int8 pipe issues at twice the bf16 rate
+        ad = ix.actual_dim
+        ops = 2.0 * nq * rows * ad
+        gemm_ms = kern_ms / max(args.steps, 1)  # all contraction launches of one step
+        achieved = ops / (gemm_ms * 1e-3) / 1e12
+        pairs = float(nq) * rows * world
+        out = {
+            "metric": "scored (query, vector) pairs/s (batched u8 dot, 4096 q x 10M x 768-d)",
+            "value": pairs * args.steps / (ms * 1e-3), "unit": "vectors/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic: torch.rand embeddings generated and encoded on the "
+            "device, seed 42 + rank; numpy default_rng(43) queries",
+            "config": {"workload": wl["name"], "rows_per_gpu": rows, "dim": dim, "k": k, "queries": nq,
+                       "sharding": f"point-id ranges x{world}",
+                       "l2": f"codes {rows * ad / 1e6:.0f} MB per GPU exceed the 126 MB L2; no flush"},
+            "e2e": {"value": pairs * args.steps / (e2e_ms * 1e-3), "unit": "vectors/s",
+                    "h2d_bytes_per_step": int(q_host.nbytes), "d2h_bytes_per_step": int(nq * k * 8),
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "u8_batch_kernel (tcgen05.mma kind::i8), all launches of a step",
+                         "kernel_ms": gemm_ms, "kernel_launches_timed": kern_n,
+                         "peak_source": "2 x measured bf16 burst (MEASURED_PEAKS.json bf16_tflops); int8 ops = 2*Q*N*K",
+                         "frac_of_nominal_4500": achieved / 4500.0},
+            "clocks": clocks,
+        }
+        if not args.no_cpu:
+            import oracle as O
+            n = min(args.cpu_sample, ix.count)
+            nqs = 8
+            storage = np.ascontiguousarray(ix.download()[: n * ix.row_bytes])
+            o = O.OracleU8(storage, n, dim, 0, False, ix.alpha, ix.offset, ix.multiplier)
+            cores = os.cpu_count() or 1
+            encs = [ix.encode_query(q_host[i]) for i in range(nqs)]
+            sub = qz.EncodedVectorsU8(ctx, storage, qz.VectorParameters(dim, n, qz.DistanceType.Dot, False), ix.alpha,
+                                      ix.offset, ix.multiplier)
+            gs, gi = sub.search_batch(q_host[:nqs], k, True)
+            par = True
+            t0 = time.perf_counter()
+            reps = 0
+            while True:
+                for i in range(nqs):
+                    os_, oi = o.search(encs[i], k, True, threads=cores)
+                    if reps == 0:
+                        par = par and bool(np.array_equal(gi[i], oi) and np.array_equal(gs[i].view(np.uint32), os_.view(np.uint32)))
+                reps += 1
+                dt = time.perf_counter() - t0
+                if dt >= 3.0:
+                    break
+            sub.close()
+            out["cpu_baseline"] = {"value": n * nqs * reps / dt, "unit": "vectors/s", "cores": cores,
+                                   "kind": "reference" if O.ref.available else "port",
+                                   "sample": f"first {n} rows of rank 0's shard x {nqs} queries, {reps} rounds of "
+                                             f"single-query scans + top-{k} (the reference has no batched path), {cores} threads, {dt:.1f} s wall",
+                                   "gpu_topk_matches_cpu_on_sample": par}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------------- reference arm
 def run_reference(args):
     """The reference's own CPU implementation of the path on the host cores: its C scorers compiled
@@ -348,7 +517,7 @@ def run_reference(args):
     wl = WORKLOADS[args.workload]
     n, dim, k = args.cpu_sample, wl["dim"], wl["k"]
     cores = os.cpu_count() or 1
-    if args.workload == "u8":
+    if args.workload in ("u8", "u8batch"):  # (the reference has no batched path: a batch is a loop of scans)
         data = O.uniform(42, n * dim).reshape(n, dim)
         o = O.OracleU8.encode(data, 0, False)
         q = o.encode_query(O.uniform(43, dim))
@@ -393,5 +562,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "u8batch":
+        run_gpu_batch(a)
     else:
         run_gpu(a)

@@ -125,6 +125,13 @@ QZ_API qz_status qz_u8_search_batch(qz_index *index, const float *queries, uint3
 QZ_API qz_status qz_u8_search_batch_dev(qz_index *index, const float *d_queries, uint32_t nq, uint32_t k,
                                         int32_t largest, float *d_scores, uint32_t *d_ids);
 
+/* Cross-shard merge for query batches: d_scores_in / d_ids_in = [n_lists][nq][k] results of
+ * qz_u8_search_batch_dev on n_lists shards (e.g. after an all-gather); outputs [nq][k].  Device pointers,
+ * asynchronous on the context stream.  n_lists * k <= 16384. */
+QZ_API qz_status qz_merge_topk_batch_dev(qz_ctx *ctx, const float *d_scores_in, const uint32_t *d_ids_in,
+                                         uint32_t n_lists, uint32_t nq, uint32_t k, int32_t largest, float *d_scores,
+                                         uint32_t *d_ids);
+
 /* ---- binary quantizer (EncodedVectorsBin, encoded_vectors_binary.rs) ------------------------- */
 
 /* bytes per row for BitsStoreType u8 (store_bytes = 1, binary.rs:99-116) or u128 (16, :152-159) */

@@ -2,11 +2,12 @@
 (encoded_vectors.rs:21-35) that are codec-independent once an index handle exists, plus the
 fused scan entry points that only make sense on the GPU (score_all / search_top_k)."""
 import ctypes as C
+import sys
 
 import numpy as np
 
 from . import _lib
-from .encoded_vectors import Context, EncodingError, default_context, ptr
+from .encoded_vectors import Context, EncodingError, _live_indexes, default_context, ptr
 
 
 class DeviceIndex:
@@ -16,6 +17,7 @@ class DeviceIndex:
         self.ctx = ctx
         self._L = ctx._L
         self.handle = None
+        _live_indexes.add(self)
 
     # ---- trait: encode_query / score_point / score_internal -------------------------------
     def encode_query(self, query):
@@ -106,6 +108,8 @@ class DeviceIndex:
             self.handle = None
 
     def __del__(self):
+        if sys.is_finalizing():
+            return
         try:
             self.close()
         except Exception:

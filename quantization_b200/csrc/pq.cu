@@ -285,6 +285,7 @@ qz_status qz_pq_index_create(qz_ctx *ctx, const uint8_t *codes, uint64_t count, 
     std::lock_guard<std::mutex> g(ctx->mu);
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     qz_index *ix = new qz_index();
+    ctx->refs.fetch_add(1);
     ix->ctx = ctx;
     ix->codec = QZ_CODEC_PQ;
     ix->count = count;
@@ -321,6 +322,7 @@ qz_status qz_pq_index_create(qz_ctx *ctx, const uint8_t *codes, uint64_t count, 
     if (st != QZ_OK) {
         cudaFree(ix->d_storage);
         pq_index_free(ix);
+        ctx->refs.fetch_sub(1);
         delete ix;
         return st;
     }

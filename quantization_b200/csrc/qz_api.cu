@@ -75,6 +75,7 @@ qz_status qz_u8_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t count
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     qz_index *ix = new qz_index();
     ix->ctx = ctx;
+    ctx->refs.fetch_add(1);
     ix->codec = QZ_CODEC_U8;
     ix->count = count;
     ix->dim = dim;
@@ -89,6 +90,7 @@ qz_status qz_u8_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t count
     qz_status st = index_alloc_storage(ix, storage);
     if (st != QZ_OK) {
         cudaFree(ix->d_storage);
+        ctx->refs.fetch_sub(1);
         delete ix;
         return st;
     }
@@ -107,14 +109,17 @@ qz_status qz_u8_index_set_params(qz_index *ix, float alpha, float offset, float 
 void qz_index_destroy(qz_index *ix) {
     if (!ix) return;
     if (ix->ctx) {
-        std::lock_guard<std::mutex> g(ix->ctx->mu);
-        cudaSetDevice(ix->ctx->device);
-        cudaStreamSynchronize(ix->ctx->stream);
-        cudaFree(ix->d_storage);
-        cudaFree(ix->d_codes_soa);
-        cudaFree(ix->d_voff_soa);
-        cudaFree(ix->d_batch);
-        pq_index_free(ix);
+        {
+            std::lock_guard<std::mutex> g(ix->ctx->mu);
+            cudaSetDevice(ix->ctx->device);
+            cudaStreamSynchronize(ix->ctx->stream);
+            cudaFree(ix->d_storage);
+            cudaFree(ix->d_codes_soa);
+            cudaFree(ix->d_voff_soa);
+            cudaFree(ix->d_batch);
+            pq_index_free(ix);
+        }
+        ctx_release(ix->ctx);  // the context outlives its indexes even if qz_ctx_destroy came first
     }
     delete ix;
 }
@@ -334,6 +339,7 @@ qz_status qz_bin_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t coun
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     qz_index *ix = new qz_index();
     ix->ctx = ctx;
+    ctx->refs.fetch_add(1);
     ix->codec = QZ_CODEC_BIN;
     ix->count = count;
     ix->dim = dim;
@@ -345,6 +351,7 @@ qz_status qz_bin_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t coun
     qz_status st = index_alloc_storage(ix, storage);
     if (st != QZ_OK) {
         cudaFree(ix->d_storage);
+        ctx->refs.fetch_sub(1);
         delete ix;
         return st;
     }

@@ -81,6 +81,10 @@ void timing_end(qz_ctx *ctx) {
     ctx->ev_head++;
 }
 
+static void ctx_free(qz_ctx *ctx);
+void ctx_release(qz_ctx *ctx) {
+    if (ctx && ctx->refs.fetch_sub(1) == 1) ctx_free(ctx);
+}
 }  // namespace qz
 
 using namespace qz;
@@ -134,6 +138,13 @@ qz_status qz_ctx_create(int32_t device, void *stream, qz_ctx **out) {
 
 void qz_ctx_destroy(qz_ctx *ctx) {
     if (!ctx) return;
+    qz::ctx_release(ctx);
+}
+
+}  // extern "C"
+
+namespace qz {
+static void ctx_free(qz_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->d_partial);
@@ -151,6 +162,9 @@ void qz_ctx_destroy(qz_ctx *ctx) {
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
+}  // namespace qz
+
+extern "C" {
 
 const char *qz_last_error(const qz_ctx *ctx) { return ctx ? ctx->err.c_str() : g_global_err.c_str(); }
 const char *qz_last_global_error(void) { return g_global_err.c_str(); }

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <mutex>
 #include <string>
 
@@ -17,6 +18,7 @@ struct qz_ctx {
     std::string err;
     uint64_t launches = 0;
     std::mutex mu;  // serialises host entry points that share the scratch below
+    std::atomic<int> refs{1};  // the context handle + every live index; freed when the last one goes
 
     // device scratch
     uint64_t *d_partial = nullptr;  // [max(sm_count,256)][QZ_MAX_K] per-CTA top-k lists
@@ -74,6 +76,7 @@ struct qz_index {
 namespace qz {
 
 qz_status fail(qz_ctx *ctx, qz_status st, const std::string &msg);
+void ctx_release(qz_ctx *ctx);  // drop one reference (qz_ctx_destroy, qz_index_destroy)
 qz_status cuda_fail(qz_ctx *ctx, cudaError_t e, const char *what);
 qz_status ensure_query(qz_ctx *ctx, size_t bytes);
 qz_status ensure_io(qz_ctx *ctx, size_t bytes);

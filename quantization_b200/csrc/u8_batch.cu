@@ -317,17 +317,8 @@ struct CompactParams {
     uint32_t *ids;  // [nq][k]
 };
 
-__global__ void __launch_bounds__(512) u8_batch_compact_kernel(CompactParams p) {
-    extern __shared__ __align__(16) uint64_t ks[];
-    const uint32_t q = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
-    uint64_t *cq = p.cand + (size_t)q * p.cap;
-    uint32_t n = p.cnt[q];
-    if (n > p.cap) n = p.cap;
-    if (!p.final_out && n <= p.k) return;  // nothing to drop yet; threshold stays
-    uint32_t P = 32;
-    while (P < n) P <<= 1;
-    for (uint32_t i = tid; i < P; i += T) ks[i] = i < n ? cq[i] : 0ull;
-    __syncthreads();
+// bitonic sort of P (power of two) keys in shared memory, descending, by the whole CTA
+__device__ __forceinline__ void block_sort_desc(uint64_t *ks, uint32_t P, uint32_t tid, uint32_t T) {
     for (uint32_t size = 2; size <= P; size <<= 1) {
         for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
             for (uint32_t t = tid; t < (P >> 1); t += T) {
@@ -342,6 +333,57 @@ __global__ void __launch_bounds__(512) u8_batch_compact_kernel(CompactParams p) 
             __syncthreads();
         }
     }
+}
+
+// Cross-shard merge for query batches: per query, G lists of k (score, id) results (e.g. the all-gathered
+// outputs of qz_u8_search_batch_dev on G ranks) -> the k best overall, same ordering contract.
+struct MergeBatchParams {
+    const float *scores_in;   // [G][nq][k]
+    const uint32_t *ids_in;   // [G][nq][k]
+    uint32_t G, nq, k, flip;
+    float *scores;            // [nq][k]
+    uint32_t *ids;            // [nq][k]
+};
+
+__global__ void __launch_bounds__(512) topk_merge_batch_kernel(MergeBatchParams p) {
+    extern __shared__ __align__(16) uint64_t ks[];
+    const uint32_t q = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+    const uint32_t n = p.G * p.k;
+    uint32_t P = 32;
+    while (P < n) P <<= 1;
+    for (uint32_t i = tid; i < P; i += T) {
+        uint64_t key = 0;
+        if (i < n) {
+            const uint32_t g = i / p.k, j = i - g * p.k;
+            const size_t at = ((size_t)g * p.nq + q) * p.k + j;
+            const uint32_t id = p.ids_in[at];
+            if (id != 0xFFFFFFFFu) key = make_key(p.scores_in[at], id, p.flip);  // 0xFFFFFFFF marks an empty slot
+        }
+        ks[i] = key;
+    }
+    __syncthreads();
+    block_sort_desc(ks, P, tid, T);
+    for (uint32_t i = tid; i < p.k; i += T) {
+        float sc;
+        uint32_t id;
+        split_key(ks[i], p.flip, sc, id);
+        p.scores[(size_t)q * p.k + i] = sc;
+        p.ids[(size_t)q * p.k + i] = id;
+    }
+}
+
+__global__ void __launch_bounds__(512) u8_batch_compact_kernel(CompactParams p) {
+    extern __shared__ __align__(16) uint64_t ks[];
+    const uint32_t q = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+    uint64_t *cq = p.cand + (size_t)q * p.cap;
+    uint32_t n = p.cnt[q];
+    if (n > p.cap) n = p.cap;
+    if (!p.final_out && n <= p.k) return;  // nothing to drop yet; threshold stays
+    uint32_t P = 32;
+    while (P < n) P <<= 1;
+    for (uint32_t i = tid; i < P; i += T) ks[i] = i < n ? cq[i] : 0ull;
+    __syncthreads();
+    block_sort_desc(ks, P, tid, T);
     const uint32_t keep = n < p.k ? n : p.k;
     for (uint32_t i = tid; i < keep; i += T) cq[i] = ks[i];
     if (tid == 0) {
@@ -523,7 +565,8 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
         do {
             uint64_t R = first;
             if (!safe && done) {
-                const uint64_t grow = done * cap / (8ull * k);
+                static const uint64_t margin = getenv("QZ_BATCH_MARGIN") ? (uint64_t)atoi(getenv("QZ_BATCH_MARGIN")) : 16ull;
+                const uint64_t grow = done * cap / (margin * k);
                 R = grow > first ? grow / kBatchN * kBatchN : first;
             }
             if (safe && done) R = (cap - k) / kBatchN * kBatchN ? (cap - k) / kBatchN * kBatchN : kBatchN;
@@ -589,6 +632,28 @@ qz_status qz_u8_search_batch_dev(qz_index *ix, const float *d_queries, uint32_t 
     std::lock_guard<std::mutex> g(ctx->mu);
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     return batch_search(ix, d_queries, nq, k, largest, d_scores, d_ids);
+}
+
+qz_status qz_merge_topk_batch_dev(qz_ctx *ctx, const float *d_scores_in, const uint32_t *d_ids_in, uint32_t n_lists,
+                                  uint32_t nq, uint32_t k, int32_t largest, float *d_scores, uint32_t *d_ids) {
+    if (!ctx) return QZ_ARGUMENTS;
+    if (k == 0 || k > QZ_MAX_K) return fail(ctx, QZ_ARGUMENTS, "merge_topk_batch: k must be in [1, QZ_MAX_K]");
+    if (nq == 0 || n_lists == 0) return QZ_OK;
+    if (!d_scores_in || !d_ids_in || !d_scores || !d_ids) return fail(ctx, QZ_ARGUMENTS, "merge_topk_batch: NULL argument");
+    if ((uint64_t)n_lists * k > 16384) return fail(ctx, QZ_ARGUMENTS, "merge_topk_batch: n_lists * k must be <= 16384");
+    QZ_CUDA(ctx, cudaSetDevice(ctx->device));
+    static bool attr = false;
+    if (!attr) {
+        QZ_CUDA(ctx, cudaFuncSetAttribute(topk_merge_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8));
+        attr = true;
+    }
+    uint32_t P = 32;
+    while (P < n_lists * k) P <<= 1;
+    MergeBatchParams mp{d_scores_in, d_ids_in, n_lists, nq, k, largest ? 0u : 0xFFFFFFFFu, d_scores, d_ids};
+    topk_merge_batch_kernel<<<nq, 512, (size_t)P * 8, ctx->stream>>>(mp);
+    QZ_CUDA(ctx, cudaGetLastError());
+    ctx->launches++;
+    return QZ_OK;
 }
 
 qz_status qz_u8_search_batch(qz_index *ix, const float *queries, uint32_t nq, uint32_t k, int32_t largest, float *scores,

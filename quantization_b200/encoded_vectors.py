@@ -1,8 +1,11 @@
 """API types of the reference crate, mirrored (quantization/src/encoded_vectors.rs:6-35,
 quantization/src/lib.rs:18-24, quantization/src/encoded_storage.rs:7-70) + the device context."""
+import atexit
 import ctypes as C
 import enum
+import sys
 import threading
+import weakref
 from dataclasses import dataclass
 
 import numpy as np
@@ -75,6 +78,26 @@ def get_vector_data(storage, index, vector_size):
     return storage[vector_size * index: vector_size * (index + 1)]
 
 
+# Native handles are released in a fixed order at interpreter exit — indexes, then contexts — before the CUDA
+# runtime or a borrowed (e.g. torch) stream is torn down; __del__ does nothing once the interpreter is finalizing.
+_live_indexes = weakref.WeakSet()
+_live_contexts = weakref.WeakSet()
+
+
+@atexit.register
+def _close_all():
+    for ix in list(_live_indexes):
+        try:
+            ix.close()
+        except Exception:
+            pass
+    for c in list(_live_contexts):
+        try:
+            c.close()
+        except Exception:
+            pass
+
+
 class Context:
     """One CUDA device + stream (qz_ctx)."""
 
@@ -86,6 +109,7 @@ class Context:
             raise EncodingError(_KIND.get(st, "EncodingError"), self._L.qz_last_global_error().decode())
         self.handle = h
         self.device = device
+        _live_contexts.add(self)
 
     def check(self, st):
         if st == _lib.QZ_OK:
@@ -120,6 +144,8 @@ class Context:
             self.handle = None
 
     def __del__(self):
+        if sys.is_finalizing():
+            return
         try:
             self.close()
         except Exception:
