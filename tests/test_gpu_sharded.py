@@ -67,7 +67,8 @@ def test_sharded_search_class_world1():
     q = ix.encode_query(O.uniform(2, dim))
     dev = torch.device("cuda", 0)
     ss = S.ShardedSearch(ix, device=dev)
-    s, i = ss.search_top_k(torch.from_numpy(q.copy()).to(dev).data_ptr(), k, True, total_count=count)
+    d_q = torch.from_numpy(q.copy()).to(dev)  # (kept alive: the call takes a raw device pointer)
+    s, i = ss.search_top_k(d_q.data_ptr(), k, True, total_count=count)
     ws, wi = o.search(q, k, True)
     assert np.array_equal(i, wi) and np.array_equal(s.view(np.uint32), ws.view(np.uint32))
     torch.cuda.set_stream(torch.cuda.default_stream(0))
