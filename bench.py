@@ -290,12 +290,11 @@ def run_gpu(args):
     # e2e: the host-buffer calls a user of the trait makes, every step: f32 query -> encode_query ->
     # scan_topk -> (scores, ids) on the host
     for _ in range(3):
-        ix.search_top_k(ix.encode_query(q_host), k, True)
+        ix.search(q_host, k, True)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        blob = ix.encode_query(q_host)
-        hs, hi = ix.search_top_k(blob, k, True)
+        hs, hi = ix.search(q_host, k, True)  # qz_search_topk: H2D query, encode_query, scan + top-k, D2H results
         if world > 1:  # host-side exchange of the k results per rank, then merge on the device
             mine = torch.from_numpy(np.concatenate([hs.view(np.uint32), hi]).astype(np.int64)).to(dev)
             allr = torch.empty(world * mine.numel(), dtype=torch.int64, device=dev)
@@ -324,8 +323,9 @@ def run_gpu(args):
                        "l2": f"input {rows * wl['row_bytes'] / 1e6:.0f} MB per GPU per step "
                              + ("exceeds" if rows * wl["row_bytes"] > 126e6 else "FITS IN") + " the 126 MB L2; no flush"},
             "e2e": {"value": total_rows * args.steps / (e2e_ms * 1e-3), "unit": "vectors/s",
-                    "h2d_bytes_per_step": int(q_host.nbytes + enc.nbytes),
-                    "d2h_bytes_per_step": int(enc.nbytes + k * 8), "ms_per_step": e2e_ms / args.steps},
+                    "h2d_bytes_per_step": int(q_host.nbytes),
+                    "d2h_bytes_per_step": int(k * 8), "ms_per_step": e2e_ms / args.steps,
+                    "call": "qz_search_topk (host f32 query -> host scores, ids), one call per step"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(args.workload) if rows == wl["rows"] else None,

@@ -211,6 +211,11 @@ QZ_API qz_status qz_scan_topk(qz_index *index, const void *enc_query, uint32_t k
 QZ_API qz_status qz_scan_topk_dev(qz_index *index, const void *d_enc_query, uint32_t k, int32_t largest,
                                   uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
 
+/* encode_query + the fused scan in one call with one synchronisation: `query` = dim f32 on the host; results as
+ * qz_scan_topk.  The end-to-end path of a caller that holds raw f32 queries. */
+QZ_API qz_status qz_search_topk(qz_index *index, const float *query, uint32_t k, int32_t largest, float *scores,
+                                uint32_t *ids, uint32_t *n_out);
+
 /* score_point for every point: out[i] = score_point(q, i), i in [0,count). */
 QZ_API qz_status qz_scan_scores(qz_index *index, const void *enc_query, float *scores);
 QZ_API qz_status qz_scan_scores_dev(qz_index *index, const void *d_enc_query, float *d_scores);

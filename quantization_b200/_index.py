@@ -69,6 +69,18 @@ class DeviceIndex:
                                             C.byref(n)))
         return scores[: n.value].copy(), ids[: n.value].copy()
 
+    def search(self, query_f32, k, largest=True):
+        """encode_query + search_top_k in one library call (one synchronisation): raw f32 query in, (scores, ids) out"""
+        q = np.ascontiguousarray(query_f32, np.float32).reshape(-1)
+        if q.size != self.vector_parameters.dim:
+            raise EncodingError("ArgumentsError", f"query length {q.size} != dim {self.vector_parameters.dim}")
+        scores = np.empty(k, np.float32)
+        ids = np.empty(k, np.uint32)
+        n = C.c_uint32(0)
+        self.ctx.check(self._L.qz_search_topk(self.handle, ptr(q), k, int(bool(largest)), ptr(scores), ptr(ids),
+                                              C.byref(n)))
+        return scores[: n.value], ids[: n.value]
+
     # ---- device-pointer forms (asynchronous on the context stream) -------------------------
     def search_top_k_dev(self, d_query, k, largest, d_keys=0, d_scores=0, d_ids=0):
         self.ctx.check(self._L.qz_scan_topk_dev(self.handle, C.c_void_p(d_query), k, int(bool(largest)),

@@ -37,6 +37,7 @@ _SIGS = {
                                      C.c_uint64, vp, vp, f32p, f32p, f32p]),
     "qz_u8_search_batch": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp]),
     "qz_u8_search_batch_dev": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp]),
+    "qz_search_topk": (C.c_int32, [vp, vp, C.c_uint32, C.c_int32, vp, vp, u32p]),
     "qz_merge_topk_batch_dev": (C.c_int32, [vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32, vp, vp]),
     "qz_bin_row_bytes": (C.c_uint32, [C.c_uint32, C.c_int32]),
     "qz_bin_index_create": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, C.c_int32, C.c_uint32,

@@ -37,10 +37,10 @@ qz_status index_alloc_storage(qz_index *ix, const uint8_t *host_storage) {
 // scan of any codec: every score to d_scores (optional) and/or per-CTA top-k lists in
 // ctx->d_partial
 static qz_status scan_any(qz_index *ix, const void *d_query, float *d_scores, uint32_t k, int largest,
-                          uint32_t *n_lists, uint32_t *Kp) {
+                          uint32_t *n_lists, uint32_t *Kp, const ScanFinal *fin = nullptr) {
     qz_ctx *ctx = ix->ctx;
     if (ix->codec == QZ_CODEC_PQ) return pq_scan(ix, d_query, d_scores, k, largest, n_lists, Kp);
-    qz_status st = launch_row_scan(ix, d_query, d_scores, k, largest, n_lists, Kp);
+    qz_status st = launch_row_scan(ix, d_query, d_scores, k, largest, n_lists, Kp, fin);
     if (st != QZ_ARGUMENTS) return st;
     // row shape outside the streaming kernel (rows that are not whole words, or huge rows):
     // warp-per-row gather kernel, then top-k over the score array
@@ -182,7 +182,10 @@ qz_status qz_scan_topk_dev(qz_index *ix, const void *d_enc_query, uint32_t k, in
     if (!d_enc_query && qz_query_bytes(ix)) return fail(ctx, QZ_ARGUMENTS, "scan_topk: NULL query");
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     uint32_t n_lists = 0, Kp = topk_pad(k);
-    if (ix->count) QZ_TRY(scan_any(ix, d_enc_query, nullptr, k, largest, &n_lists, &Kp));
+    bool fused = false;
+    const ScanFinal fin{d_keys, d_scores, d_ids, &fused};
+    if (ix->count) QZ_TRY(scan_any(ix, d_enc_query, nullptr, k, largest, &n_lists, &Kp, &fin));
+    if (fused) return QZ_OK;
     return launch_merge(ctx, ctx->d_partial, n_lists, Kp, Kp, k, largest, d_keys, d_scores, d_ids);
 }
 
@@ -205,6 +208,38 @@ qz_status qz_scan_topk(qz_index *ix, const void *enc_query, uint32_t k, int32_t 
     QZ_TRY(qz_scan_topk_dev(ix, ctx->d_query, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
     float *hs = reinterpret_cast<float *>(ctx->h_pin + qb_pad);
     uint32_t *hi = reinterpret_cast<uint32_t *>(ctx->h_pin + qb_pad + (size_t)k * 4);
+    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    QZ_CUDA(ctx, cudaMemcpyAsync(hi, ctx->d_ids_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const uint32_t m = (uint32_t)(ix->count < k ? ix->count : k);
+    memcpy(scores, hs, (size_t)m * 4);
+    memcpy(ids, hi, (size_t)m * 4);
+    if (n_out) *n_out = m;
+    return QZ_OK;
+}
+
+qz_status qz_search_topk(qz_index *ix, const float *query, uint32_t k, int32_t largest, float *scores, uint32_t *ids,
+                         uint32_t *n_out) {
+    if (bad_index(ix)) return QZ_ARGUMENTS;
+    qz_ctx *ctx = ix->ctx;
+    if (!scores || !ids) return fail(ctx, QZ_ARGUMENTS, "search_topk: NULL output");
+    if (k == 0 || k > QZ_MAX_K) return fail(ctx, QZ_ARGUMENTS, "search_topk: k must be in [1, QZ_MAX_K]");
+    const size_t qb = qz_query_bytes(ix), fb = (size_t)ix->dim * sizeof(float);
+    if (fb && !query) return fail(ctx, QZ_ARGUMENTS, "search_topk: NULL query");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    QZ_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t fb_pad = (fb + 255) / 256 * 256, qb_pad = (qb + 255) / 256 * 256;
+    QZ_TRY(ensure_query(ctx, fb_pad + qb_pad + 16));
+    QZ_TRY(ensure_pin(ctx, fb_pad + (size_t)k * 8));
+    uint8_t *d_f32 = ctx->d_query, *d_blob = ctx->d_query + fb_pad;
+    if (fb && qb) {
+        memcpy(ctx->h_pin, query, fb);
+        QZ_CUDA(ctx, cudaMemcpyAsync(d_f32, ctx->h_pin, fb, cudaMemcpyHostToDevice, ctx->stream));
+        QZ_TRY(qz_encode_query_dev(ix, reinterpret_cast<const float *>(d_f32), 1, d_blob));
+    }
+    QZ_TRY(qz_scan_topk_dev(ix, d_blob, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
+    float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
+    uint32_t *hi = reinterpret_cast<uint32_t *>(ctx->h_pin + fb_pad + (size_t)k * 4);
     QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaMemcpyAsync(hi, ctx->d_ids_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -124,6 +124,8 @@ qz_status qz_ctx_create(int32_t device, void *stream, qz_ctx **out) {
     const size_t lists = ctx->sm_count > 256 ? ctx->sm_count : 256;
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_partial, lists * QZ_MAX_K * sizeof(uint64_t));
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_merge_tmp, (size_t)256 * QZ_MAX_K * sizeof(uint64_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_done, 256);
+    if (e == cudaSuccess) e = cudaMemset(ctx->d_done, 0, 256);
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_keys, QZ_MAX_K * sizeof(uint64_t));
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_scores_k, QZ_MAX_K * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_ids_k, QZ_MAX_K * sizeof(uint32_t));
@@ -149,6 +151,7 @@ static void ctx_free(qz_ctx *ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->d_partial);
     cudaFree(ctx->d_merge_tmp);
+    cudaFree(ctx->d_done);
     cudaFree(ctx->d_keys);
     cudaFree(ctx->d_scores_k);
     cudaFree(ctx->d_ids_k);

@@ -23,6 +23,7 @@ struct qz_ctx {
     // device scratch
     uint64_t *d_partial = nullptr;  // [max(sm_count,256)][QZ_MAX_K] per-CTA top-k lists
     uint64_t *d_merge_tmp = nullptr;
+    uint32_t *d_done = nullptr;     // CTA arrival counter of the scan's in-launch merge (zero between launches)
     uint64_t *d_keys = nullptr;     // [QZ_MAX_K]
     float *d_scores_k = nullptr;    // [QZ_MAX_K]
     uint32_t *d_ids_k = nullptr;    // [QZ_MAX_K]
@@ -105,8 +106,14 @@ static inline uint32_t pow2_ceil(uint32_t v) {
 static inline uint32_t topk_pad(uint32_t k) { return pow2_ceil(k < 128 ? 128 : k); }
 
 // scans (row_scan.cu)
+struct ScanFinal {  // where the scan kernel's in-launch final merge writes (each pointer may be NULL)
+    uint64_t *d_keys;
+    float *d_scores;
+    uint32_t *d_ids;
+    bool *fused;  // out: the kernel did the final merge
+};
 qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, uint32_t k, int largest,
-                          uint32_t *n_lists, uint32_t *Kp_out);
+                          uint32_t *n_lists, uint32_t *Kp_out, const ScanFinal *fin = nullptr);
 // merge (topk.cu): lists at d_in -> final keys/scores/ids
 qz_status launch_merge(qz_ctx *ctx, const uint64_t *d_in, uint32_t n_lists, uint32_t in_len, uint32_t in_stride,
                        uint32_t k, int largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);

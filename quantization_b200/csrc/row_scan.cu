@@ -65,8 +65,10 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
 // Launch the scan of a u8 or binary index.  d_scores (optional) receives every score;
 // if k > 0 the per-CTA top-k lists land in ctx->d_partial ([*n_lists][*Kp_out]).
 // Returns QZ_ARGUMENTS with a message if the row shape is not supported by this kernel.
+// With `fin` (k > 0) the kernel also merges the lists and writes the final results, when the merge's work
+// area fits the ring; *fin->fused tells the caller whether it still has to call launch_merge.
 qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, uint32_t k, int largest,
-                          uint32_t *n_lists, uint32_t *Kp_out) {
+                          uint32_t *n_lists, uint32_t *Kp_out, const ScanFinal *fin) {
     qz_ctx *ctx = ix->ctx;
     const uint32_t Kp = k ? topk_pad(k) : 128;
     const uint32_t hdr = ix->codec == QZ_CODEC_U8 ? 1 : 0;
@@ -97,6 +99,31 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     p.flip = largest ? 0u : 0xFFFFFFFFu;
     p.id_base = ix->id_base;
     uint32_t grid = pl.n_tiles < (uint32_t)ctx->sm_count ? pl.n_tiles : (uint32_t)ctx->sm_count;
+    if (fin) *fin->fused = false;
+    static const bool env_nofuse = getenv("QZ_SCAN_NO_FUSED_MERGE") != nullptr;
+    if (fin && k && !env_nofuse && grid <= kPruneMaxLists) {
+        const uint32_t lpc = pow2_ceil(grid < 2 ? 2 : grid);
+        size_t need = (size_t)(lpc / 2) * Kp * 8;
+        if (need < kPruneSmem) need = kPruneSmem;
+        if (need <= (size_t)pl.n_slots * pl.slot_bytes) {
+            MergeParams &m = p.merge;
+            m.in = ctx->d_partial;
+            m.n_lists = grid;
+            m.in_len = Kp;
+            m.in_stride = Kp;
+            m.Kp = Kp;
+            m.lists_per_cta = lpc;
+            m.out = nullptr;
+            m.final_out = 1;
+            m.k = k;
+            m.flip = p.flip;
+            m.keys = fin->d_keys;
+            m.scores = fin->d_scores;
+            m.ids = fin->d_ids;
+            p.done = ctx->d_done;
+            *fin->fused = true;
+        }
+    }
     cudaError_t e;
     timing_begin(ctx);
     if (ix->codec == QZ_CODEC_BIN) e = launch_row_scan_xor(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);

@@ -51,6 +51,10 @@ struct RowScanParams {
     float *scores;          // optional [count]
     uint64_t *partial;      // optional [gridDim.x][Kp]
     uint32_t k, Kp, flip, id_base;
+    // final merge inside this launch (done != NULL): the CTA that finishes last reduces all gridDim.x partial
+    // lists to the final top-k with its consumer warps.  merge.in = partial, merge.n_lists = gridDim.x.
+    uint32_t *done;  // zero before the launch; the last CTA leaves it zero again
+    MergeParams merge;
 };
 
 template <int OP>
@@ -274,6 +278,22 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
         named_bar_sync(1, kConsumerWarps * 32);
         uint64_t *out = p.partial + (size_t)blockIdx.x * p.Kp;
         for (uint32_t i = threadIdx.x; i < p.Kp; i += kConsumerWarps * 32) out[i] = top[i];
+        if (p.done) {
+            // last-CTA-done: publish this list, count, and let the last arrival merge them all.  Every bulk copy
+            // of this CTA has been consumed, so the ring is free to serve as the merge's work area.
+            __threadfence();
+            named_bar_sync(1, kConsumerWarps * 32);
+            if (threadIdx.x == 0) {
+                const uint32_t prev = atomicAdd(p.done, 1u);
+                __threadfence();
+                *lock = prev == gridDim.x - 1;
+            }
+            named_bar_sync(1, kConsumerWarps * 32);
+            if (*lock) {
+                prune_merge<1, true>(p.merge, reinterpret_cast<uint64_t *>(ring), threadIdx.x, kConsumerWarps * 32);
+                if (threadIdx.x == 0) *p.done = 0;
+            }
+        }
     }
 }
 

@@ -246,9 +246,24 @@ struct MergeParams {
     uint32_t *ids;
 };
 
+// The merge bodies below run either as a whole CTA (BAR == 0: __syncthreads) or as a thread group of
+// T threads with ranks tid = 0..T-1 inside a bigger CTA (BAR > 0: named barrier BAR), which is how the
+// single-query scan runs its final merge in its last CTA (row_scan.cuh).  CG: read the input lists with
+// ld.global.cg (they were written by other CTAs of the same launch).
+template <int BAR>
+__device__ __forceinline__ void grp_sync(uint32_t T) {
+    if (BAR == 0) __syncthreads();
+    else named_bar_sync(BAR, T);
+}
+template <bool CG>
+__device__ __forceinline__ uint64_t ld_list(const uint64_t *ptr) {
+    return CG ? (uint64_t)__ldcg(reinterpret_cast<const unsigned long long *>(ptr)) : *ptr;
+}
+
 // first k keys of s[0..have) -> keys / scores / ids outputs (slots past `have` are empty)
-__device__ __forceinline__ void write_final(const MergeParams &p, const uint64_t *s, uint32_t have) {
-    for (uint32_t i = threadIdx.x; i < p.k; i += blockDim.x) {
+__device__ __forceinline__ void write_final(const MergeParams &p, const uint64_t *s, uint32_t have, uint32_t tid,
+                                            uint32_t T) {
+    for (uint32_t i = tid; i < p.k; i += T) {
         const uint64_t key = i < have ? s[i] : 0ull;
         if (p.keys) p.keys[i] = key;
         float sc;
@@ -259,20 +274,20 @@ __device__ __forceinline__ void write_final(const MergeParams &p, const uint64_t
     }
 }
 
-__device__ __forceinline__ void tree_merge(const MergeParams &p, uint64_t *s) {
-    const uint32_t tid = threadIdx.x, T = blockDim.x;
+template <int BAR, bool CG>
+__device__ __forceinline__ void tree_merge(const MergeParams &p, uint64_t *s, uint32_t tid, uint32_t T, uint32_t blk) {
     const uint32_t Kp = p.Kp, half = Kp >> 1;
-    const uint32_t first = blockIdx.x * p.lists_per_cta;
+    const uint32_t first = blk * p.lists_per_cta;
     uint32_t nl = p.lists_per_cta >> 1;  // lists resident in smem after the load level
     // level 0: fused load + pairwise max
     for (uint32_t idx = tid; idx < nl * Kp; idx += T) {
         uint32_t pr = idx / Kp, i = idx - pr * Kp;
         uint32_t la = first + 2 * pr, lb = la + 1, j = Kp - 1 - i;
-        uint64_t a = (la < p.n_lists && i < p.in_len) ? p.in[(size_t)la * p.in_stride + i] : 0ull;
-        uint64_t b = (lb < p.n_lists && j < p.in_len) ? p.in[(size_t)lb * p.in_stride + j] : 0ull;
+        uint64_t a = (la < p.n_lists && i < p.in_len) ? ld_list<CG>(p.in + (size_t)la * p.in_stride + i) : 0ull;
+        uint64_t b = (lb < p.n_lists && j < p.in_len) ? ld_list<CG>(p.in + (size_t)lb * p.in_stride + j) : 0ull;
         s[idx] = a > b ? a : b;
     }
-    __syncthreads();
+    grp_sync<BAR>(T);
     uint32_t step = 1;  // distance (in lists) between live lists
     for (;;) {
         // bitonic merge of every live list (descending)
@@ -282,7 +297,7 @@ __device__ __forceinline__ void tree_merge(const MergeParams &p, uint64_t *s) {
                 uint32_t lo = sub * step * Kp + 2 * tt - (tt & (stride - 1));
                 ce_desc(s, (int)lo, (int)(lo + stride));
             }
-            __syncthreads();
+            grp_sync<BAR>(T);
         }
         if (nl == 1) break;
         // pairwise max of live lists (in place: result lands in the first list of each pair)
@@ -294,44 +309,47 @@ __device__ __forceinline__ void tree_merge(const MergeParams &p, uint64_t *s) {
             if (b > a) A[i] = b;
         }
         step <<= 1;
-        __syncthreads();
+        grp_sync<BAR>(T);
     }
     if (p.out) {
-        for (uint32_t i = tid; i < p.out_len; i += T) p.out[(size_t)blockIdx.x * p.out_stride + i] = i < Kp ? s[i] : 0ull;
+        for (uint32_t i = tid; i < p.out_len; i += T) p.out[(size_t)blk * p.out_stride + i] = i < Kp ? s[i] : 0ull;
     }
-    if (p.final_out) write_final(p, s, Kp);
+    if (p.final_out) write_final(p, s, Kp, tid, T);
 }
 
 template <int kUnused = 0>
 __global__ void __launch_bounds__(1024, 1) merge_lists_kernel(MergeParams p) {
     extern __shared__ __align__(16) uint64_t s[];
-    tree_merge(p, s);
+    tree_merge<0, false>(p, s, threadIdx.x, blockDim.x, blockIdx.x);
 }
 
 // ---------------------------------------------------------------------------------------------
-// Final merge with pruning (one CTA).  The lists are sorted, so for any position j the m-th
+// Final merge with pruning (one thread group).  The lists are sorted, so for any position j the m-th
 // largest of {list_g[j]} has at least m*(j+1) elements at or above it: with m*(j+1) >= k that is
 // a lower bound T on the k-th best key overall.  Only keys >= T (typically a few hundred out of
-// n_lists*k) are gathered and bitonic-sorted.  If more than kPruneCap survive (adversarial
-// inputs) the exact tree merge above runs instead, in the same launch.
+// n_lists*k) are gathered and sorted.  If more than kPruneCap survive (adversarial inputs) the exact
+// tree merge above runs instead, in the same launch.
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t kPruneCap = 2048;
 constexpr uint32_t kPruneMaxLists = 256;
 
-// dynamic shared memory the pruned path needs: sort area + staged survivors + their ranks
-constexpr size_t kPruneSmem = (size_t)kPruneCap * (8 + 8 + 4);
+struct PruneShared {
+    uint64_t vals[kPruneMaxLists];
+    uint64_t wmax[kPruneMaxLists / 32];
+    uint64_t thrA;
+    uint32_t ranks[kPruneMaxLists];
+    uint32_t cnt, pad;
+};
+// shared memory the pruned path needs: sort area + staged survivors + their ranks + the block above
+constexpr size_t kPruneSmem = (size_t)kPruneCap * (8 + 8 + 4) + sizeof(PruneShared);
 
-template <int kUnused = 0>
-__global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
-    extern __shared__ __align__(16) uint64_t s[];  // max(kPruneSmem, tree-merge need)
-    __shared__ uint64_t vals[kPruneMaxLists];
-    __shared__ uint32_t ranks[kPruneMaxLists];
-    __shared__ uint64_t wmax[kPruneMaxLists / 32];
-    __shared__ uint64_t thrA;
-    __shared__ uint32_t cnt;
+// s: max(kPruneSmem, tree-merge need) bytes, 16-byte aligned.  Needs 256 <= T, T a multiple of 256... (T = 512, 1024)
+template <int BAR, bool CG>
+__device__ __forceinline__ void prune_merge(const MergeParams &p, uint64_t *s, uint32_t tid, uint32_t T) {
     uint64_t *cand = s + kPruneCap;
     uint32_t *rk = reinterpret_cast<uint32_t *>(cand + kPruneCap);
-    const uint32_t tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5;
+    PruneShared &sh = *reinterpret_cast<PruneShared *>(rk + kPruneCap);
+    const uint32_t lane = tid & 31, warp = tid >> 5;
     const uint32_t G = p.n_lists;
     // probe A: position jp1-1 and the m-th largest value there, m*jp1 >= k, m <= G
     // probe B: position k-1, m = 1 (the best list's k-th key)
@@ -341,70 +359,92 @@ __global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
     const bool probeA = G > 0 && jp1 <= p.in_len && m <= G;
     const bool probeB = G > 0 && p.k <= p.in_len;
     if (tid == 0) {
-        thrA = 0ull;
-        cnt = 0;
+        sh.thrA = 0ull;
+        sh.cnt = 0;
     }
     if (tid < kPruneMaxLists) {
         uint64_t a = 0, b = 0;
         if (tid < G) {
-            if (probeA) a = p.in[(size_t)tid * p.in_stride + (jp1 - 1)];
-            if (probeB) b = p.in[(size_t)tid * p.in_stride + (p.k - 1)];
+            if (probeA) a = ld_list<CG>(p.in + (size_t)tid * p.in_stride + (jp1 - 1));
+            if (probeB) b = ld_list<CG>(p.in + (size_t)tid * p.in_stride + (p.k - 1));
         }
-        vals[tid] = a;
-        ranks[tid] = 0;
+        sh.vals[tid] = a;
+        sh.ranks[tid] = 0;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const uint64_t b2 = __shfl_xor_sync(0xffffffffu, b, o);
             b = b2 > b ? b2 : b;
         }
-        if (lane == 0) wmax[warp] = b;
+        if (lane == 0) sh.wmax[warp] = b;
     }
-    __syncthreads();
+    // first 32 positions of this warp's first 8 lists: in flight while the threshold is computed
+    const uint32_t nw = T >> 5;
+    uint64_t kk[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+        const uint32_t l = warp + u * nw;
+        kk[u] = (l < G && lane < p.in_len) ? ld_list<CG>(p.in + (size_t)l * p.in_stride + lane) : 0ull;
+    }
+    grp_sync<BAR>(T);
     uint64_t thrB = 0;
 #pragma unroll
-    for (uint32_t w = 0; w < kPruneMaxLists / 32; w++) thrB = wmax[w] > thrB ? wmax[w] : thrB;
+    for (uint32_t w = 0; w < kPruneMaxLists / 32; w++) thrB = sh.wmax[w] > thrB ? sh.wmax[w] : thrB;
     if (probeA) {  // rank every probe value; the comparison loop is split over T / Gp threads per value
         uint32_t Gp = 32;
         while (Gp < G) Gp <<= 1;
         const uint32_t parts = T / Gp, g = tid % Gp, part = tid / Gp;
         if (g < G) {
-            const uint64_t mine = vals[g];
+            const uint64_t mine = sh.vals[g];
             const uint32_t per = (G + parts - 1) / parts;
             const uint32_t h0 = part * per, h1 = min(h0 + per, G);
             uint32_t r = 0;
             for (uint32_t h = h0; h < h1; h++) {
-                const uint64_t v = vals[h];
+                const uint64_t v = sh.vals[h];
                 r += (v > mine) || (v == mine && h < g);
             }
-            if (r) atomicAdd(&ranks[g], r);
+            if (r) atomicAdd(&sh.ranks[g], r);
         }
-        __syncthreads();
-        if (tid < G && ranks[tid] == m - 1) thrA = vals[tid];
+        grp_sync<BAR>(T);
+        if (tid < G && sh.ranks[tid] == m - 1) sh.thrA = sh.vals[tid];
     }
-    __syncthreads();
-    const uint64_t Tkey = thrA > thrB ? thrA : thrB;
+    grp_sync<BAR>(T);
+    const uint64_t Tkey = sh.thrA > thrB ? sh.thrA : thrB;
     // the survivors of a sorted list are a prefix: one warp per list, 32 positions per step
-    for (uint32_t l = warp; l < G; l += T / 32) {
-        const uint64_t *lp = p.in + (size_t)l * p.in_stride;
-        for (uint32_t i0 = 0; i0 < p.in_len; i0 += 32) {
-            const uint32_t i = i0 + lane;
-            const uint64_t key = i < p.in_len ? lp[i] : 0ull;
-            const bool pass = key != 0 && key >= Tkey;
-            const uint32_t mk = __ballot_sync(0xffffffffu, pass);
-            if (mk) {
-                uint32_t pos0 = 0;
-                if (lane == 0) pos0 = atomicAdd(&cnt, (uint32_t)__popc(mk));
-                pos0 = __shfl_sync(0xffffffffu, pos0, 0);
-                const uint32_t pos = pos0 + __popc(mk & ((1u << lane) - 1));
-                if (pass && pos < kPruneCap) cand[pos] = key;
+    for (uint32_t l0 = warp; l0 < G; l0 += nw * 8) {
+        if (l0 != warp) {
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const uint32_t l = l0 + u * nw;
+                kk[u] = (l < G && lane < p.in_len) ? ld_list<CG>(p.in + (size_t)l * p.in_stride + lane) : 0ull;
             }
-            if (mk != 0xffffffffu) break;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const uint32_t l = l0 + u * nw;
+            if (l >= G) break;
+            const uint64_t *lp = p.in + (size_t)l * p.in_stride;
+            uint64_t key = kk[u];
+            for (uint32_t i0 = 0;;) {
+                const bool pass = key != 0 && key >= Tkey;
+                const uint32_t mk = __ballot_sync(0xffffffffu, pass);
+                if (mk) {
+                    uint32_t pos0 = 0;
+                    if (lane == 0) pos0 = atomicAdd(&sh.cnt, (uint32_t)__popc(mk));
+                    pos0 = __shfl_sync(0xffffffffu, pos0, 0);
+                    const uint32_t pos = pos0 + __popc(mk & ((1u << lane) - 1));
+                    if (pass && pos < kPruneCap) cand[pos] = key;
+                }
+                i0 += 32;
+                if (mk != 0xffffffffu || i0 >= p.in_len) break;
+                key = i0 + lane < p.in_len ? ld_list<CG>(lp + i0 + lane) : 0ull;
+            }
         }
     }
-    __syncthreads();
-    const uint32_t n = cnt;
+    grp_sync<BAR>(T);
+    const uint32_t n = sh.cnt;
     if (n > kPruneCap) {  // not prunable: the exact tree merge, in the same launch (uniform branch)
-        tree_merge(p, s);
+        grp_sync<BAR>(T);  // everyone has read n before the tree merge overwrites the area
+        tree_merge<BAR, CG>(p, s, tid, T, 0);
         return;
     }
     if (n <= 512) {
@@ -413,7 +453,7 @@ __global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
             if (i < p.k) s[i] = 0ull;
             if (i < 512) rk[i] = 0;
         }
-        __syncthreads();
+        grp_sync<BAR>(T);
         uint32_t np = 32;
         while (np < n) np <<= 1;
         const uint32_t parts = T / np, e = tid % np, part = tid / np;
@@ -425,16 +465,16 @@ __global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
             for (uint32_t h = h0; h < h1; h++) r += cand[h] > mine;
             if (r) atomicAdd(&rk[e], r);
         }
-        __syncthreads();
+        grp_sync<BAR>(T);
         if (tid < n && rk[tid] < p.k) s[rk[tid]] = cand[tid];
-        __syncthreads();
-        write_final(p, s, p.k);
+        grp_sync<BAR>(T);
+        write_final(p, s, p.k, tid, T);
         return;
     }
     uint32_t P = 1024;
     while (P < n) P <<= 1;
     for (uint32_t i = tid; i < P; i += T) s[i] = i < n ? cand[i] : 0ull;
-    __syncthreads();
+    grp_sync<BAR>(T);
     for (uint32_t size = 2; size <= P; size <<= 1) {
         for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
             for (uint32_t t = tid; t < (P >> 1); t += T) {
@@ -442,10 +482,16 @@ __global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
                 if ((lo & size) == 0 || size == P) ce_desc(s, (int)lo, (int)(lo + stride));
                 else ce_asc(s, (int)lo, (int)(lo + stride));
             }
-            __syncthreads();
+            grp_sync<BAR>(T);
         }
     }
-    write_final(p, s, P);
+    write_final(p, s, P, tid, T);
+}
+
+template <int kUnused = 0>
+__global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
+    extern __shared__ __align__(16) uint64_t s[];  // max(kPruneSmem, tree-merge need)
+    prune_merge<0, false>(p, s, threadIdx.x, blockDim.x);
 }
 
 }  // namespace qz

@@ -219,3 +219,13 @@ def test_sharded_ids(ctx):
     ms, mi = O.merge_topk(np.concatenate([r[0] for r in res]), np.concatenate([r[1] for r in res]), 64, True)
     os_, oi = o.search(gq, 64, True)
     assert np.array_equal(mi, oi) and np.array_equal(bits(ms), bits(os_))
+
+
+def test_search_fused_call(ctx):
+    """qz_search_topk == encode_query + scan_topk"""
+    data, query = make(3000, 200)
+    for dist in DISTS:
+        g, o = encode_both(ctx, data, dist, False)
+        s, i = g.search(query, 50, dist == qz.DistanceType.Dot)
+        ws, wi = o.search(o.encode_query(query), 50, dist == qz.DistanceType.Dot)
+        assert np.array_equal(i, wi) and np.array_equal(bits(s), bits(ws))
