@@ -7,7 +7,8 @@
 namespace qz {
 
 struct ScanPlan {
-    uint32_t tile_rows, slot_bytes, n_slots, wpl;
+    uint32_t tile_rows, slot_bytes, n_slots, n_groups, wpl, lpr;
+    bool vec;  // binary rows scored with the 8-lanes-per-row vector mapping (kOpXorV)
     uint32_t n_tiles;
     bool full;
     size_t smem;
@@ -16,6 +17,7 @@ struct ScanPlan {
 cudaError_t launch_row_scan_dot(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
 cudaError_t launch_row_scan_l1(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
 cudaError_t launch_row_scan_xor(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
+cudaError_t launch_row_scan_xorv(uint32_t, uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
 
 static const int kWplSet[] = {1, 2, 3, 4, 6, 8, 12, 16, 24, 32};
 
@@ -23,14 +25,18 @@ static const int kWplSet[] = {1, 2, 3, 4, 6, 8, 12, 16, 24, 32};
 // Ring geometry: slots of ~24 KB (16 rows of the 1536-d u8 layout); the slot count is a power of two
 // (16 / n_slots consumer warps are bound to each slot).  hbm_probe (profiles/r1_hbm_probe.txt): 4-8
 // slots of 24 KB per SM sustain 7.0-7.3 TB/s of bulk copies; many small slots do not.
+// `small_rows` (binary codec): the scan is instruction-heavy per byte, so a warp group must not wait for its own
+// refill: 16 slots of ~12 KB, 8 groups, each group alternating between two slots.  (u8 rows: 8 slots of ~24 KB,
+// one per group, measured at the HBM ceiling.)
 static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes, uint32_t code_words, uint32_t Kp,
-                          ScanPlan *pl) {
+                          bool small_rows, ScanPlan *pl) {
     if (row_bytes == 0 || row_bytes % 4 != 0 || code_words == 0 || code_words > 32 * 32) return false;
     if (count >= 0xFFFFFFFFull) return false;
     static const uint32_t env_target = getenv("QZ_SCAN_TILE_BYTES") ? atoi(getenv("QZ_SCAN_TILE_BYTES")) : 0;
     static const uint32_t env_align = getenv("QZ_SCAN_ROW_ALIGN") ? atoi(getenv("QZ_SCAN_ROW_ALIGN")) : 0;
     static const uint32_t env_slots = getenv("QZ_SCAN_SLOTS") ? atoi(getenv("QZ_SCAN_SLOTS")) : 0;
-    const uint32_t target = env_target ? env_target : 24832;
+    static const uint32_t env_groups = getenv("QZ_SCAN_GROUPS") ? atoi(getenv("QZ_SCAN_GROUPS")) : 0;
+    const uint32_t target = env_target ? env_target : (small_rows ? 12416 : 24832);
     const uint32_t align = env_align ? env_align : kTileRowAlign;
     uint32_t tile_rows = (target / row_bytes) / align * align;
     if (tile_rows < align) tile_rows = align;
@@ -42,8 +48,13 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
     if (ctx->smem_optin < fixed + (size_t)slot_bytes) return false;
     uint32_t fit = (uint32_t)((ctx->smem_optin - fixed) / slot_bytes);
     uint32_t n_slots = 1;
-    const uint32_t max_slots = env_slots ? env_slots : 8;
-    while (n_slots * 2 <= fit && n_slots * 2 <= max_slots) n_slots *= 2;
+    const uint32_t max_slots = env_slots ? env_slots : (small_rows ? 16 : 8);
+    while (n_slots * 2 <= fit && n_slots * 2 <= max_slots && n_slots * 2 <= (uint32_t)kMaxSlots) n_slots *= 2;
+    uint32_t n_groups = env_groups ? pow2_ceil(env_groups) : 8;
+    if (n_groups > (uint32_t)kConsumerWarps) n_groups = kConsumerWarps;
+    if (n_groups > n_slots) n_groups = n_slots;
+    pl->vec = small_rows && row_bytes % 16 == 0 && row_bytes <= 512 && !getenv("QZ_SCAN_NO_VEC");
+    pl->lpr = 8;
     uint32_t need = (code_words + 31) / 32;
     uint32_t wpl = 0;
     for (int w : kWplSet)
@@ -52,11 +63,31 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
             break;
         }
     if (!wpl) return false;
+    pl->full = code_words == 32 * wpl;
+    pl->lpr = 8;
+    if (pl->vec) {
+        const uint32_t row_vec = row_bytes / 16;
+        // 4 lanes per row when two consecutive rows then fall into disjoint bank halves (stride = 64 mod 128 bytes)
+        static const uint32_t env_lpr = getenv("QZ_SCAN_LPR") ? atoi(getenv("QZ_SCAN_LPR")) : 0;
+        pl->lpr = env_lpr ? env_lpr : ((row_vec % 8 == 4 && row_vec <= 16) ? 4 : 8);
+        wpl = (row_vec + pl->lpr - 1) / pl->lpr;  // 16-byte vectors per lane
+        pl->full = row_vec == pl->lpr * wpl;
+        if (wpl > 4) pl->vec = false;
+    }
+    if (!pl->vec) {
+        wpl = 0;
+        for (int w : kWplSet)
+            if ((uint32_t)w >= need) {
+                wpl = w;
+                break;
+            }
+        pl->full = code_words == 32 * wpl;
+    }
     pl->tile_rows = tile_rows;
     pl->slot_bytes = slot_bytes;
     pl->n_slots = n_slots;
+    pl->n_groups = n_groups;
     pl->wpl = wpl;
-    pl->full = code_words == 32 * wpl;
     pl->n_tiles = (uint32_t)((count + tile_rows - 1) / tile_rows);
     pl->smem = fixed + (size_t)n_slots * slot_bytes;
     return true;
@@ -74,7 +105,7 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     const uint32_t hdr = ix->codec == QZ_CODEC_U8 ? 1 : 0;
     const uint32_t code_words = ix->row_bytes / 4 - hdr;
     ScanPlan pl;
-    if (!plan_row_scan(ctx, ix->count, ix->row_bytes, code_words, Kp, &pl))
+    if (!plan_row_scan(ctx, ix->count, ix->row_bytes, code_words, Kp, ix->codec == QZ_CODEC_BIN, &pl))
         return fail(ctx, QZ_ARGUMENTS, "row shape not supported by the streaming scan kernel");
     RowScanParams p{};
     p.storage = ix->d_storage;
@@ -86,6 +117,11 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     p.tile_rows = pl.tile_rows;
     p.slot_bytes = pl.slot_bytes;
     p.n_slots = pl.n_slots;
+    p.n_groups = pl.n_groups;
+    // u8 CTAs see a few thousand rows: 512 unfiltered rows buy a threshold good enough that no warp ever fills its
+    // staging buffer.  Binary CTAs see ~70k rows: a longer warm-up keeps the buffers from filling all at once.
+    static const uint32_t env_warm = getenv("QZ_SCAN_WARM") ? atoi(getenv("QZ_SCAN_WARM")) : 0;
+    p.warm_rows = env_warm ? env_warm : (ix->codec == QZ_CODEC_BIN ? 2048 : 512);
     p.n_tiles = pl.n_tiles;
     p.query = reinterpret_cast<const uint32_t *>(d_query);
     p.multiplier = ix->multiplier;
@@ -126,7 +162,8 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     }
     cudaError_t e;
     timing_begin(ctx);
-    if (ix->codec == QZ_CODEC_BIN) e = launch_row_scan_xor(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
+    if (ix->codec == QZ_CODEC_BIN && pl.vec) e = launch_row_scan_xorv(pl.lpr, pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
+    else if (ix->codec == QZ_CODEC_BIN) e = launch_row_scan_xor(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
     else if (ix->distance == QZ_L1) e = launch_row_scan_l1(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
     else e = launch_row_scan_dot(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
     timing_end(ctx);

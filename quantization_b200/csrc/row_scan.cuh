@@ -26,11 +26,15 @@
 namespace qz {
 
 constexpr int kOpDot = 0, kOpL1 = 1, kOpXor = 2;
+// kOpXorV / kOpXorV4: xor-popcount with 8 / 4 lanes per row reading 16-byte vectors (rows that are whole 16-byte
+// units): 4 / 8 rows per warp step, two steps per batch, a 3- / 2-level reduction instead of the 5-level row
+// butterfly.  For these mappings WPL counts 16-byte vectors per lane.  The host picks the lane count that keeps
+// the LDS.128 quarter-warps bank-conflict free (4 lanes when the row stride is 64 mod 128 bytes).
+constexpr int kOpXorV = 3, kOpXorV4 = 4;
 constexpr int kConsumerWarps = 16;
 constexpr int kScanThreads = (kConsumerWarps + 1) * 32;
 constexpr int kMaxSlots = 16;
 constexpr int kBatchRows = 8;    // rows one warp scores per step
-constexpr int kWarmRows = 512;    // rows per CTA scored before the first top-k threshold exists
 constexpr int kTileRowAlign = 16;  // tiles are 16-row multiples => every tile starts 16-byte aligned
 
 struct RowScanParams {
@@ -43,7 +47,11 @@ struct RowScanParams {
     uint32_t tile_rows;      // multiple of 16
     uint32_t slot_bytes;     // >= tile_rows*row_bytes, multiple of 128
     uint32_t n_slots;        // power of two, <= 16
+    uint32_t n_groups;       // consumer warp groups (power of two, divides n_slots): group g drains local tiles
+                             // g, g + n_groups, ...; with n_slots = 2 * n_groups a group's next tile is in
+                             // flight while it works on the current one
     uint32_t n_tiles;
+    uint32_t warm_rows;      // rows per CTA scored before the first top-k threshold exists (<= 2048)
     const uint32_t *query;  // device blob: u8 [f32 offset][codes], binary [bits]
     float multiplier;       // u8
     uint32_t dim;           // binary
@@ -79,8 +87,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool do_topk = p.partial != nullptr;
-    const uint32_t n_slots = p.n_slots;
-    const uint32_t warps_per_slot = kConsumerWarps / n_slots;
+    const uint32_t n_slots = p.n_slots, n_groups = p.n_groups;
+    const uint32_t warps_per_slot = kConsumerWarps / n_groups;  // warps that share a tile
 
     if (threadIdx.x == 0) {
         for (uint32_t s = 0; s < n_slots; s++) {
@@ -122,13 +130,26 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     }
 
     // ---------------- consumers: warps_per_slot warps share each slot ----------------
-    uint32_t q[WPL];
+    constexpr bool kVec = OP == kOpXorV || OP == kOpXorV4;
+    constexpr int kLpr = OP == kOpXorV4 ? 4 : 8;                // lanes per row (vector mappings)
+    constexpr int kRps = 32 / kLpr;                             // rows per warp step
+    constexpr int kRowsB = kVec ? 2 * kRps : kBatchRows;        // rows per batch
+    const uint32_t lsub = lane & (kLpr - 1), lgrp = lane / kLpr;
+    constexpr int kQ = kVec ? 4 * WPL : WPL;  // query words a lane keeps in registers
+    uint32_t q[kQ];
     bool jv[WPL];
 #pragma unroll
     for (int j = 0; j < WPL; j++) {
-        const uint32_t w = lane + 32 * j;
-        jv[j] = FULL || w < p.code_words;
-        q[j] = jv[j] ? __ldg(p.query + p.hdr_words + w) : 0u;
+        if (kVec) {
+            const uint32_t v = lsub + kLpr * j;  // 16-byte vector of the row this lane owns
+            jv[j] = FULL || 4 * v < p.code_words;
+#pragma unroll
+            for (int c = 0; c < 4; c++) q[(4 * j + c) % kQ] = jv[j] ? __ldg(p.query + 4 * v + c) : 0u;
+        } else {
+            const uint32_t w = lane + 32 * j;
+            jv[j] = FULL || w < p.code_words;
+            q[j] = jv[j] ? __ldg(p.query + p.hdr_words + w) : 0u;
+        }
     }
     const float q_off = p.hdr_words ? __uint_as_float(__ldg(p.query)) : 0.0f;
 
@@ -137,10 +158,13 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     int cnt = 0;
     const uint32_t rw = p.row_words;
     const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4;
-    const uint32_t rr = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);  // row this lane reports
-    const uint32_t slot = warp / warps_per_slot, member = warp - slot * warps_per_slot;
-    const uint32_t *sl = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * p.slot_bytes);
-    const uint32_t batch_stride = warps_per_slot * kBatchRows;
+    // row (of the 8-row batch) this lane reports, and whether it reports at all (8 reporters per warp)
+    const uint32_t rr = kVec ? lgrp + (lsub ? kRps : 0)
+                             : ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    const bool reporter = kVec ? lsub < 2 : !(lane & 3);
+    const uint32_t group = warp / warps_per_slot, member = warp - group * warps_per_slot;
+    const uint32_t slot_mask = n_slots - 1, slot_shift = __ffs(n_slots) - 1;
+    const uint32_t batch_stride = warps_per_slot * kRowsB;
 
     // Top-k warm-up (k <= 128): the keys of the CTA's first `warm_tiles` tiles go unfiltered into the
     // staging area (one slot per row, no atomics); then the consumer warps together reduce them to
@@ -149,19 +173,19 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     // stall the whole ring (measured: +80 us on a 218 us scan).
     const bool coop = do_topk && p.Kp == (uint32_t)kCandPerWarp;
     uint32_t warm_rounds = 0;
-    if (coop && n_slots * p.tile_rows <= (uint32_t)(kConsumerWarps * kCandPerWarp)) {
-        const uint32_t per_round = n_slots * p.tile_rows;
-        warm_rounds = (kWarmRows + per_round - 1) / per_round;
+    if (coop && n_groups * p.tile_rows <= (uint32_t)(kConsumerWarps * kCandPerWarp)) {
+        const uint32_t per_round = n_groups * p.tile_rows;
+        warm_rounds = (p.warm_rows + per_round - 1) / per_round;
         if (warm_rounds * per_round > (uint32_t)(kConsumerWarps * kCandPerWarp))
             warm_rounds = (kConsumerWarps * kCandPerWarp) / per_round;
     }
 
-    uint32_t parity = 0, round = 0;
+    uint32_t round = 0;
     bool warm = warm_rounds > 0;
-    for (uint32_t t = slot;; t += n_slots, parity ^= 1, round++) {
+    for (uint32_t t = group;; t += n_groups, round++) {
         if (warm && round == warm_rounds) {
             // ---- end of warm-up: cooperative reduction of the staged keys (all consumer warps) ----
-            uint32_t tiles_w = warm_rounds * n_slots;
+            uint32_t tiles_w = warm_rounds * n_groups;
             if (tiles_w > my_tiles) tiles_w = my_tiles;
             const uint32_t n_keys = tiles_w * p.tile_rows;
             const uint32_t n_chunks = (n_keys + kCandPerWarp - 1) / kCandPerWarp;
@@ -179,13 +203,39 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             if (warm) continue;  // (fewer tiles than warm-up rounds: keep counting rounds up to the barrier)
             break;
         }
-        mbar_wait(&full[slot], parity);
+        const uint32_t slot = t & slot_mask;
+        const uint32_t *sl = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * p.slot_bytes);
+        mbar_wait(&full[slot], (t >> slot_shift) & 1);
         const uint32_t row0 = (blockIdx.x + t * gridDim.x) * p.tile_rows;
         const uint32_t left = p.count - row0;
         const uint32_t rows_valid = left < p.tile_rows ? left : p.tile_rows;
         const uint32_t rows_iter = warm ? p.tile_rows : rows_valid;  // warm-up also writes the empty keys of missing rows
 
-        for (uint32_t b = member * kBatchRows; b < rows_iter; b += batch_stride) {
+        for (uint32_t b = member * kRowsB; b < rows_iter; b += batch_stride) {
+            uint32_t total;
+            if (kVec) {
+                // rows b + lgrp and b + kRps + lgrp; lsub picks the 16-byte vectors
+                const uint4 *r0 = reinterpret_cast<const uint4 *>(sl + (b + lgrp) * rw) + lsub;
+                const uint4 *r1 = reinterpret_cast<const uint4 *>(sl + (b + kRps + lgrp) * rw) + lsub;
+                uint32_t a0 = 0, a1 = 0;
+#pragma unroll
+                for (int j = 0; j < WPL; j++) {
+                    if (FULL || jv[j]) {
+                        const uint4 v0 = r0[kLpr * j], v1 = r1[kLpr * j];
+                        const int qb = (4 * j) % kQ;
+                        a0 += __popc(v0.x ^ q[qb]) + __popc(v0.y ^ q[qb + 1]) + __popc(v0.z ^ q[qb + 2]) +
+                              __popc(v0.w ^ q[qb + 3]);
+                        a1 += __popc(v1.x ^ q[qb]) + __popc(v1.y ^ q[qb + 1]) + __popc(v1.z ^ q[qb + 2]) +
+                              __popc(v1.w ^ q[qb + 3]);
+                    }
+                }
+#pragma unroll
+                for (int o = kLpr / 2; o > 0; o >>= 1) {
+                    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+                    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+                }
+                total = lsub ? a1 : a0;
+            } else {
             uint32_t acc[kBatchRows];
 #pragma unroll
             for (int r = 0; r < kBatchRows; r++) acc[r] = 0;
@@ -213,17 +263,19 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
                 acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
             }
             acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 2);
-            const uint32_t total = acc[0] + __shfl_xor_sync(0xffffffffu, acc[0], 1);
+            total = acc[0] + __shfl_xor_sync(0xffffffffu, acc[0], 1);
+            }
 
-            // epilogue: one row per lane group of 4 (lane & 3 == 0 reports)
+            // epilogue: 8 reporting lanes per warp, one row each
             const uint32_t rit = b + rr;
-            const bool valid = !(lane & 3) && rit < rows_valid;
+            const bool valid = reporter && rit < rows_valid;
             float score;
-            if (OP == kOpXor) {
-                // calculate_metric, encoded_vectors_binary.rs:237-252 (all values small integers, exact)
-                const float x = __uint2float_rn(total);
-                const float z = __fsub_rn(__uint2float_rn(p.dim), x);
-                score = p.bin_zx ? __fsub_rn(z, x) : __fsub_rn(x, z);
+            if (OP == kOpXor || kVec) {
+                // calculate_metric, encoded_vectors_binary.rs:237-252: zeros = dim - xor, then zeros - xor or
+                // xor - zeros in f32.  Every value is an integer below 2^24, so the f32 steps are exact and equal
+                // to converting the integer difference once.
+                const int d2 = (int)p.dim - 2 * (int)total;
+                score = __int2float_rn(p.bin_zx ? d2 : -d2);
             } else {
                 // multiplier * S + query.offset + vector_offset, left to right, no FMA (u8.rs:347)
                 const float vo = __uint_as_float(sl[rit * rw]);
@@ -234,15 +286,31 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             if (do_topk) {
                 const uint64_t key = make_key(score, p.id_base + grow, p.flip);
                 if (warm) {
-                    if (!(lane & 3)) cand_all[t * p.tile_rows + rit] = valid ? key : 0ull;
+                    if (reporter) cand_all[t * p.tile_rows + rit] = valid ? key : 0ull;
                 } else {
                     const bool pass = valid && key > *thr;
                     const uint32_t m = __ballot_sync(0xffffffffu, pass);
                     if (m) {
                         const int n = __popc(m);
                         if (cnt + n > kCandPerWarp) {
-                            cta_topk_flush(st, cand, cnt, lane);
-                            cnt = 0;
+                            // staging full.  The threshold has usually risen since these keys were staged (another
+                            // warp flushed): drop what no longer passes, and only take the CTA lock if that did
+                            // not free half of the buffer
+                            const uint64_t th = *thr;
+                            int kept = 0;
+                            for (int base = 0; base < cnt; base += 32) {
+                                const uint64_t c = base + (int)lane < cnt ? cand[base + lane] : 0ull;
+                                const bool keep = c > th;
+                                const uint32_t mk = __ballot_sync(0xffffffffu, keep);
+                                if (keep) cand[kept + __popc(mk & ((1u << lane) - 1))] = c;
+                                kept += __popc(mk);
+                                __syncwarp();
+                            }
+                            cnt = kept;
+                            if (cnt + n > kCandPerWarp / 2) {
+                                cta_topk_flush(st, cand, cnt, lane);
+                                cnt = 0;
+                            }
                         }
                         if (pass) cand[cnt + __popc(m & ((1u << lane) - 1))] = key;
                         cnt += n;

@@ -50,6 +50,27 @@ def test_binary_reference_shapes(ctx, store, dim, dist, invert):
     assert np.array_equal(gi, oi) and np.array_equal(bits(gs_k), bits(os_k))
 
 
+@pytest.mark.parametrize("dim", [256, 384, 768, 1024, 1536, 2048, 2560, 3072, 4096, 4224])
+def test_binary_vector_mappings(ctx, dim):
+    """u128 rows of 2..33 16-byte vectors: every lanes-per-row / vectors-per-lane variant of the scan
+    (full and masked), several tiles per CTA with a ragged last tile, scores and top-k bit-exact"""
+    count = 40_037
+    data = O.uniform(11 + dim, count * dim, -1.0, 1.0).reshape(count, dim)
+    query = O.uniform(12 + dim, dim, -1.0, 1.0)
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
+    g = qz.EncodedVectorsBin.encode(data, qz.VecStorageBuilder(), vp, ctx=ctx)
+    o = O.OracleBin.encode(data, 0, False, 16)
+    assert np.array_equal(np.asarray(g.encoded_vectors), o.storage)
+    gq, oq = g.encode_query(query), o.encode_query(query)
+    ref = o.scan(oq)
+    assert np.array_equal(bits(g.score_all(gq)), bits(ref))
+    for largest in (True, False):
+        for k in (1, 100, 128, 300):
+            gs_k, gi = g.search_top_k(gq, k, largest)
+            os_k, oi = o.search(oq, k, largest)
+            assert np.array_equal(gi, oi) and np.array_equal(bits(gs_k), bits(os_k))
+
+
 def test_binary_massive_ties_large(ctx):
     """<= dim+1 distinct scores over 200k rows: the id tie-break is load bearing"""
     count, dim = 200_000, 256
