@@ -8,6 +8,7 @@
 //
 // Centroids live on the device "chunk-major": ct[bounds[ch]*256 + c*len + t] = centroids[c][bounds[ch]+t],
 // so one chunk's 256 sub-centroids are contiguous.
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -16,6 +17,10 @@
 #include "common.cuh"
 
 namespace qz {
+
+bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32_t n_chunks, uint32_t n_slices,
+                     const float *d_perm, float *d_scores, uint32_t k, int largest, uint32_t id_base, uint32_t *n_lists,
+                     cudaError_t *err);
 
 constexpr int kPqCentroids = 256;     // CENTROIDS_COUNT, pq.rs:25
 constexpr int kSliceChunks = 128;     // chunks per LUT slice: 32 lanes x 4 code bytes
@@ -223,6 +228,27 @@ qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, 
     dim3 pg(8, slices);
     pq_lut_permute_kernel<<<pg, 256, 0, ctx->stream>>>((const float *)d_lut, ix->n_chunks, ix->d_lut_perm);
     QZ_TRY(check_launch(ctx, "pq_lut_permute_kernel"));
+    // streaming kernel (pq_scan2.cu): k <= 128 is reduced inside the kernel; otherwise the final scores go to
+    // partial[0] and the generic top-k pass runs over that one part
+    static const bool env_v1 = getenv("QZ_PQ_V1") != nullptr;
+    if (!env_v1) {
+        const bool fused = k > 0 && k <= 128;
+        float *sc = fused ? d_scores : (d_scores ? d_scores : ix->d_pq_partial);
+        cudaError_t e2 = cudaSuccess;
+        uint32_t lists = 0;
+        if (pq_scan2_launch(ctx, ix->d_storage, ix->count, ix->n_chunks, slices, ix->d_lut_perm, sc, fused ? k : 0, largest,
+                            ix->id_base, &lists, &e2)) {
+            if (e2 != cudaSuccess) return cuda_fail(ctx, e2, "pq_scan2_kernel");
+            ctx->launches++;
+            if (fused) {
+                if (n_lists) *n_lists = lists;
+                if (Kp_out) *Kp_out = 128;
+                return QZ_OK;
+            }
+            if (!k) return QZ_OK;
+            return launch_scores_topk(ctx, sc, 1, ix->count, ix->count, nullptr, k, largest, ix->id_base, n_lists, Kp_out);
+        }
+    }
     PqScanParams p{ix->d_storage, ix->count, ix->n_chunks, ix->d_lut_perm, ix->d_pq_partial,
                    (ix->n_chunks % 4 == 0) ? 1 : 0};
     uint32_t gx = (uint32_t)ctx->sm_count / slices;

@@ -1,0 +1,277 @@
+// pq_scan2.cu — EncodedVectorsPQ full scan, streaming version.
+//
+// score_point for every row (encoded_vectors_pq.rs:405-494): score = sum over chunks of lut[ch*256 + code[ch]].
+// The query LUT (n_chunks x 256 f32, 768 KiB at 1536-d / chunk 2) does not fit one SM's shared memory, so the
+// chunk axis is cut into slices of 128 chunks (128 KiB of LUT, bank-permuted by pq_lut_permute_kernel: lane w
+// owns code word w of the slice and all four of its gathers fall in bank w, whatever the codes).
+//
+// One persistent CTA per SM owns blocks of `block_rows` consecutive rows.  For a block it walks the slices in
+// order: the slice's LUT is bulk-copied into shared memory, a producer thread streams the block's 128-byte
+// code sub-rows through a ring of 64-row tiles (2-D TMA tiles of the row-major code matrix, completing on
+// mbarriers), sixteen consumer warps gather and add, and the per-row sums accumulate in shared memory in slice
+// order.  After the last slice the block's scores are final: they are written out (4 B per row) for the top-k
+// pass, and/or (k <= 128) reduced on the spot to the CTA's running top-k list: keys above the current threshold are
+// compacted into the (idle) LUT area and reduced with the cooperative register sorting networks of topk.cuh.
+// HBM traffic = the codes, once; nothing else leaves the SM but the final scores or the k best keys.
+// (The first version read codes with plain loads, kept per-slice partial sums in global memory and was
+// latency-bound at 2.2 TB/s)
+#include <cuda.h>
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "qz_internal.h"
+#include "topk.cuh"
+#include "tensor_map.h"
+
+namespace qz {
+
+constexpr int kPq2SliceChunks = 128;
+constexpr int kPq2SliceFloats = kPq2SliceChunks * 256;  // 128 KiB
+constexpr int kPq2TileRows = 64;
+constexpr int kPq2TileBytes = kPq2TileRows * kPq2SliceChunks;  // 8 KiB
+constexpr int kPq2Warps = 16;                                   // consumers; warp 16 = producer
+constexpr int kPq2Groups = 4;                                   // 4 warps x 16 rows share a tile
+constexpr int kPq2Threads = (kPq2Warps + 1) * 32;
+
+struct PqScan2Params {
+    uint64_t count;
+    uint32_t n_slices, n_slots;
+    uint32_t block_rows;  // multiple of 64
+    uint32_t n_blocks;
+    const float *perm;  // [n_slices][kPq2SliceFloats]
+    float *scores;      // optional [count]
+    uint64_t *partial;  // optional [gridDim.x][128]: the CTA's 128 best keys, best first (fused top-k, k <= 128)
+    uint32_t k, flip, id_base;
+};
+
+__device__ __forceinline__ void pq2_tma_tile(void *dst, const CUtensorMap *map, int32_t c0, int32_t c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+__global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_constant__ CUtensorMap map, const PqScan2Params p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    float *slut = reinterpret_cast<float *>(smem);
+    uint8_t *ring = smem + (size_t)kPq2SliceFloats * 4;
+    float *acc = reinterpret_cast<float *>(ring + (size_t)p.n_slots * kPq2TileBytes);
+    uint64_t *full = reinterpret_cast<uint64_t *>(acc + p.block_rows);
+    uint64_t *empty = full + p.n_slots;
+    uint64_t *lutbar = empty + p.n_slots;
+    uint64_t *top = lutbar + 1;                                  // [128] running best keys of this CTA
+    uint32_t *n_cand = reinterpret_cast<uint32_t *>(top + 128);  // append cursor of the candidate area
+    const bool do_topk = p.partial != nullptr;
+
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (uint32_t s = 0; s < p.n_slots; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], kPq2Warps / kPq2Groups);
+        }
+        mbar_init(lutbar, 1);
+        fence_mbar_init();
+    }
+    if (threadIdx.x < 128) top[threadIdx.x] = 0ull;
+    __syncthreads();
+
+    const uint32_t tiles_pb = p.block_rows / kPq2TileRows;  // tiles per (block, slice)
+    const uint32_t my_blocks = blockIdx.x < p.n_blocks ? (p.n_blocks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (warp == kPq2Warps) {
+        // ---------------- producer ----------------
+        if (lane == 0) {
+            uint32_t slot = 0, round = 0;
+            for (uint32_t lb = 0; lb < my_blocks; lb++) {
+                const uint64_t row0 = (uint64_t)(blockIdx.x + lb * gridDim.x) * p.block_rows;
+                for (uint32_t s = 0; s < p.n_slices; s++) {
+                    for (uint32_t t = 0; t < tiles_pb; t++) {
+                        if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
+                        mbar_arrive_expect_tx(&full[slot], kPq2TileBytes);
+                        // rows past `count` are out of bounds for the tensor map: zero filled, never stored
+                        pq2_tma_tile(ring + (size_t)slot * kPq2TileBytes, &map, (int32_t)(s * kPq2SliceChunks),
+                                     (int32_t)(row0 + (uint64_t)t * kPq2TileRows), &full[slot]);
+                        if (++slot == p.n_slots) {
+                            slot = 0;
+                            round++;
+                        }
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumers ----------------
+    const uint32_t group = warp / (kPq2Warps / kPq2Groups), member = warp % (kPq2Warps / kPq2Groups);
+    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2;
+    const float *my = slut + lane;
+    uint32_t seq = 0;       // tiles issued by the producer before the current (block, slice)
+    uint32_t lut_phase = 0;
+    for (uint32_t lb = 0; lb < my_blocks; lb++) {
+        const uint64_t row0 = (uint64_t)(blockIdx.x + lb * gridDim.x) * p.block_rows;
+        for (uint32_t s = 0; s < p.n_slices; s++, seq += tiles_pb) {
+            // every consumer is done with the previous slice's LUT (and, at s == 0, has stored the previous block)
+            // (the top-k phase writes candidate keys into the LUT area with ordinary stores: order them before the
+            // bulk copy's writes)
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            named_bar_sync(1, kPq2Warps * 32);
+            if (threadIdx.x == 0) {
+                mbar_arrive_expect_tx(lutbar, kPq2SliceFloats * 4);
+                const char *src = reinterpret_cast<const char *>(p.perm + (size_t)s * kPq2SliceFloats);
+                for (int i = 0; i < 4; i++)
+                    bulk_g2s(reinterpret_cast<char *>(slut) + i * 32768, src + i * 32768, 32768, lutbar);
+            }
+            mbar_wait(lutbar, lut_phase);
+            lut_phase ^= 1;
+            for (uint32_t t = group; t < tiles_pb; t += kPq2Groups) {
+                const uint32_t T = seq + t, slot = T % p.n_slots, use = T / p.n_slots;
+                mbar_wait(&full[slot], use & 1);
+                const uint32_t *tile = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * kPq2TileBytes);
+                uint32_t cw[16];
+#pragma unroll
+                for (int r = 0; r < 16; r++) cw[r] = tile[(member * 16 + r) * 32 + lane];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[slot]);  // the codes are in registers: the slot can be refilled
+                float a[16];
+#pragma unroll
+                for (int r = 0; r < 16; r++) {
+                    float v = my[((cw[r] & 0xFFu)) * 32];
+                    v = __fadd_rn(v, my[(256 + ((cw[r] >> 8) & 0xFFu)) * 32]);
+                    v = __fadd_rn(v, my[(512 + ((cw[r] >> 16) & 0xFFu)) * 32]);
+                    v = __fadd_rn(v, my[(768 + (cw[r] >> 24)) * 32]);
+                    a[r] = v;
+                }
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    float keep = upper16 ? a[i + 8] : a[i], send = upper16 ? a[i] : a[i + 8];
+                    a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 16));
+                }
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    float keep = upper8 ? a[i + 4] : a[i], send = upper8 ? a[i] : a[i + 4];
+                    a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 8));
+                }
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    float keep = upper4 ? a[i + 2] : a[i], send = upper4 ? a[i] : a[i + 2];
+                    a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 4));
+                }
+                {
+                    float keep = upper2 ? a[1] : a[0], send = upper2 ? a[0] : a[1];
+                    a[0] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 2));
+                }
+                const float total = __fadd_rn(a[0], __shfl_xor_sync(0xffffffffu, a[0], 1));
+                if (!(lane & 1)) {
+                    const uint32_t r = t * kPq2TileRows + member * 16 + (lane >> 1);
+                    acc[r] = s == 0 ? total : __fadd_rn(acc[r], total);  // slice order: ((p0 + p1) + p2) + ...
+                }
+            }
+        }
+        // the block's scores are final
+        named_bar_sync(1, kPq2Warps * 32);
+        const uint64_t left = p.count - row0;
+        const uint32_t n = left < p.block_rows ? (uint32_t)left : p.block_rows;
+        if (p.scores)
+            for (uint32_t i = threadIdx.x; i < n; i += kPq2Warps * 32) p.scores[row0 + i] = acc[i];
+        if (do_topk) {
+            // The LUT area is idle until the next slice load: candidate keys go there.  cand[0..128) = the running
+            // list, then every key of this block above the current threshold (all of them for the first block).
+            uint64_t *cand = reinterpret_cast<uint64_t *>(slut);
+            const uint64_t thr = top[p.k - 1];
+            if (threadIdx.x < 128) cand[threadIdx.x] = top[threadIdx.x];
+            if (threadIdx.x == 0) *n_cand = 128;
+            named_bar_sync(1, kPq2Warps * 32);
+            for (uint32_t i0 = 0; i0 < n; i0 += kPq2Warps * 32) {
+                const uint32_t i = i0 + threadIdx.x;
+                uint64_t key = 0;
+                if (i < n) key = make_key(acc[i], p.id_base + (uint32_t)(row0 + i), p.flip);
+                const bool pass = i < n && key > thr;
+                const uint32_t mk = __ballot_sync(0xffffffffu, pass);
+                if (mk) {
+                    uint32_t pos0 = 0;
+                    if (lane == 0) pos0 = atomicAdd(n_cand, (uint32_t)__popc(mk));
+                    pos0 = __shfl_sync(0xffffffffu, pos0, 0);
+                    if (pass) cand[pos0 + __popc(mk & ((1u << lane) - 1))] = key;
+                }
+            }
+            named_bar_sync(1, kPq2Warps * 32);
+            uint32_t nc = *n_cand;
+            // windows of 2048 keys -> their 128 best at the window start -> packed -> again, until one window is left
+            for (;;) {
+                const uint32_t nw = (nc + 2047) / 2048;
+                for (uint32_t w = 0; w < nw; w++) {
+                    const uint32_t nk = nc - w * 2048 < 2048 ? nc - w * 2048 : 2048;
+                    coop_top128(cand + (size_t)w * 2048, nk, (nk + 127) / 128, warp, lane);
+                }
+                if (nw == 1) break;
+                for (uint32_t i = 128 + threadIdx.x; i < nw * 128; i += kPq2Warps * 32)
+                    cand[i] = cand[(size_t)(i >> 7) * 2048 + (i & 127)];
+                named_bar_sync(1, kPq2Warps * 32);
+                nc = nw * 128;
+            }
+            if (threadIdx.x < 128) top[threadIdx.x] = cand[threadIdx.x];
+            // (the barrier at the top of the next slice / after the loop orders this against the next LUT load)
+        }
+    }
+    if (do_topk) {
+        named_bar_sync(1, kPq2Warps * 32);
+        if (threadIdx.x < 128) p.partial[(size_t)blockIdx.x * 128 + threadIdx.x] = top[threadIdx.x];
+    }
+}
+
+// Picks the geometry and launches.  Returns false when the shape is outside this kernel (row pitch not a
+// multiple of 16 bytes: no tensor map) — the caller then uses the first-generation kernel.
+// k == 0: scores only.  0 < k <= 128: the per-CTA lists go to ctx->d_partial ([*n_lists][128]) and d_scores is optional.
+bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32_t n_chunks, uint32_t n_slices,
+                     const float *d_perm, float *d_scores, uint32_t k, int largest, uint32_t id_base, uint32_t *n_lists,
+                     cudaError_t *err) {
+    *err = cudaSuccess;
+    if (n_chunks % 16 != 0 || count == 0 || count > 0x7FFFFFFFull) return false;
+    static bool attr_done = false;
+    if (!attr_done) {
+        *err = cudaFuncSetAttribute(pq_scan2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)227 * 1024);
+        if (*err != cudaSuccess) return true;
+        attr_done = true;
+    }
+    CUtensorMap map;
+    if (!make_tensor_map_u8_2d(&map, d_codes, count, n_chunks, kPq2SliceChunks, kPq2TileRows, CU_TENSOR_MAP_SWIZZLE_NONE))
+        return false;
+    PqScan2Params p{};
+    p.count = count;
+    p.n_slices = n_slices;
+    p.perm = d_perm;
+    p.scores = d_scores;
+    p.partial = k ? ctx->d_partial : nullptr;
+    p.k = k ? k : 1;
+    p.flip = largest ? 0u : 0xFFFFFFFFu;
+    p.id_base = id_base;
+    static const uint32_t env_slots = getenv("QZ_PQ_SLOTS") ? atoi(getenv("QZ_PQ_SLOTS")) : 0;
+    static const uint32_t env_block = getenv("QZ_PQ_BLOCK_ROWS") ? atoi(getenv("QZ_PQ_BLOCK_ROWS")) : 0;
+    // n_slots must be a multiple of the group count: a slot then always serves the same warp group, so no waiter
+    // can be two phases ahead of a slot's mbarrier (with 6 slots a fast group passed the parity wait of a tile two
+    // fills ahead while the other group's fill was still in flight: launch failure, mbarrier over-arrival)
+    p.n_slots = env_slots ? env_slots / kPq2Groups * kPq2Groups : 8;
+    if (p.n_slots == 0) p.n_slots = kPq2Groups;
+    if (p.n_slots > 8) p.n_slots = 8;
+    const size_t fixed = (size_t)kPq2SliceFloats * 4 + (size_t)p.n_slots * kPq2TileBytes + (2 * p.n_slots + 1) * 8 + 128 * 8 + 16 + 1024;
+    const uint32_t max_block = (uint32_t)((ctx->smem_optin - fixed) / 4 / kPq2TileRows * kPq2TileRows);
+    // one block per CTA when the corpus is small enough for that, else blocks of the largest size that fits
+    uint64_t per_cta = (count + ctx->sm_count - 1) / ctx->sm_count;
+    per_cta = (per_cta + kPq2TileRows - 1) / kPq2TileRows * kPq2TileRows;
+    p.block_rows = per_cta < max_block ? (uint32_t)per_cta : max_block;
+    if (env_block) p.block_rows = env_block / kPq2TileRows * kPq2TileRows;
+    if (p.block_rows == 0 || p.block_rows > max_block) p.block_rows = max_block;
+    p.n_blocks = (uint32_t)((count + p.block_rows - 1) / p.block_rows);
+    const uint32_t grid = p.n_blocks < (uint32_t)ctx->sm_count ? p.n_blocks : (uint32_t)ctx->sm_count;
+    const size_t smem = fixed + (size_t)p.block_rows * 4;
+    timing_begin(ctx);
+    pq_scan2_kernel<<<grid, kPq2Threads, smem, ctx->stream>>>(map, p);
+    timing_end(ctx);
+    *err = cudaGetLastError();
+    if (n_lists) *n_lists = grid;
+    return true;
+}
+
+}  // namespace qz

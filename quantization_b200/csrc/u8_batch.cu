@@ -8,6 +8,7 @@
 
 #include "qz_internal.h"
 #include "u8_batch.cuh"
+#include "tensor_map.h"
 
 namespace qz {
 
@@ -408,33 +409,9 @@ __global__ void __launch_bounds__(512) u8_batch_compact_kernel(CompactParams p) 
 // ---------------------------------------------------------------------------------------------
 using namespace qz;
 
-typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static PFN_encodeTiled get_encode_tiled() {
-    static PFN_encodeTiled fn = nullptr;
-    if (!fn) {
-        void *p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<PFN_encodeTiled>(p);
-    }
-    return fn;
-}
-
 // 2-D u8 tensor [rows][K] (K contiguous), box = 128 bytes x box_rows, 128-byte swizzle, OOB reads give 0
 static bool make_map(CUtensorMap *map, const void *base, uint64_t rows, uint32_t K, uint32_t box_rows) {
-    PFN_encodeTiled enc = get_encode_tiled();
-    if (!enc) return false;
-    cuuint64_t dims[2] = {K, rows};
-    cuuint64_t strides[1] = {K};
-    cuuint32_t box[2] = {(cuuint32_t)kBatchKC, box_rows};
-    cuuint32_t estr[2] = {1, 1};
-    return enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    return make_tensor_map_u8_2d(map, base, rows, K, kBatchKC, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

@@ -141,6 +141,30 @@ def test_pq_shapes_topk(ctx, dim, chunk):
     assert bounds.size - 1 == g.row_bytes
 
 
+@pytest.mark.parametrize("dim,chunk,count", [(32, 2, 1_300_003), (2048, 8, 60_001), (320, 1, 9_000)])
+def test_pq_streaming_scan_blocks(ctx, dim, chunk, count):
+    """the streaming scan kernel at sizes where a CTA owns several row blocks (count > 148 x block), with 1, 2
+    and 3 LUT slices and a ragged last tile: scores within 1e-5 relative of the oracle's x86-order sums, and the
+    in-kernel top-k (k <= 128) / generic top-k (k > 128) exactly the top-k of the GPU's own scores"""
+    n_chunks = (dim + chunk - 1) // chunk
+    rng = np.random.default_rng(dim + count)
+    codes = rng.integers(0, 256, size=(count, n_chunks), dtype=np.uint8)
+    cen = O.uniform(77, 256 * dim).reshape(256, dim)
+    query = O.uniform(78, dim)
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
+    g = qz.EncodedVectorsPQ(ctx, codes.reshape(-1), vp, chunk, cen)
+    glut = g.encode_query(query)
+    lut = glut.view(np.float32).reshape(n_chunks, 256)
+    gs = g.score_all(glut)
+    ref = lut[np.arange(n_chunks)[None, :], codes].astype(np.float64).sum(1)
+    assert np.abs(gs - ref).max() <= 1e-5 * np.abs(lut).max(1).sum()
+    for largest in (True, False):
+        for k in (1, 100, 128, 200):
+            k_s, k_i = g.search_top_k(glut, k, largest)
+            e_s, e_i = O.topk(gs, k, largest)
+            assert np.array_equal(k_i, e_i) and np.array_equal(bits(k_s), bits(e_s))
+
+
 def test_pq_kmeans_training(ctx):
     """real k-means on the device (count > 256): reference tolerance + quantization error no worse than
     the CPU oracle's k-means by more than 2%"""
