@@ -330,7 +330,7 @@ def run_gpu(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(args.workload) if rows == wl["rows"] else None,
                          "kernel": {"u8": "row_scan_kernel<dot,12,full>", "bin": "row_scan_kernel<xor 4 lanes/row,3,full>",
-                                                     "pq": "pq_scan_kernel"}[args.workload],
+                                                     "pq": "pq_scan2_kernel"}[args.workload],
                          "kernel_ms": scan_ms, "kernel_launches_timed": kern_n, "peak_source": peak_src,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "clocks": clocks,

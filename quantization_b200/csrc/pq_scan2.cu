@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
     // ---------------- consumers ----------------
     const uint32_t group = warp / (kPq2Warps / kPq2Groups), member = warp % (kPq2Warps / kPq2Groups);
     const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2;
-    const float *my = slut + lane;
+    const char *my = reinterpret_cast<const char *>(slut + lane);
     uint32_t seq = 0;       // tiles issued by the producer before the current (block, slice)
     uint32_t lut_phase = 0;
     for (uint32_t lb = 0; lb < my_blocks; lb++) {
@@ -137,10 +137,12 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
                 float a[16];
 #pragma unroll
                 for (int r = 0; r < 16; r++) {
-                    float v = my[((cw[r] & 0xFFu)) * 32];
-                    v = __fadd_rn(v, my[(256 + ((cw[r] >> 8) & 0xFFu)) * 32]);
-                    v = __fadd_rn(v, my[(512 + ((cw[r] >> 16) & 0xFFu)) * 32]);
-                    v = __fadd_rn(v, my[(768 + (cw[r] >> 24)) * 32]);
+                    // one PRMT (byte extract) + one scaled add per gather address; entry (b, code) of this lane's
+                    // column sits at byte (b*256 + code) * 128 + lane * 4
+                    float v = *reinterpret_cast<const float *>(my + __byte_perm(cw[r], 0, 0x4440) * 128u);
+                    v = __fadd_rn(v, *reinterpret_cast<const float *>(my + 32768 + __byte_perm(cw[r], 0, 0x4441) * 128u));
+                    v = __fadd_rn(v, *reinterpret_cast<const float *>(my + 65536 + __byte_perm(cw[r], 0, 0x4442) * 128u));
+                    v = __fadd_rn(v, *reinterpret_cast<const float *>(my + 98304 + __byte_perm(cw[r], 0, 0x4443) * 128u));
                     a[r] = v;
                 }
 #pragma unroll
@@ -179,39 +181,49 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
             // The LUT area is idle until the next slice load: candidate keys go there.  cand[0..128) = the running
             // list, then every key of this block above the current threshold (all of them for the first block).
             uint64_t *cand = reinterpret_cast<uint64_t *>(slut);
-            const uint64_t thr = top[p.k - 1];
-            if (threadIdx.x < 128) cand[threadIdx.x] = top[threadIdx.x];
-            if (threadIdx.x == 0) *n_cand = 128;
-            named_bar_sync(1, kPq2Warps * 32);
-            for (uint32_t i0 = 0; i0 < n; i0 += kPq2Warps * 32) {
-                const uint32_t i = i0 + threadIdx.x;
-                uint64_t key = 0;
-                if (i < n) key = make_key(acc[i], p.id_base + (uint32_t)(row0 + i), p.flip);
-                const bool pass = i < n && key > thr;
-                const uint32_t mk = __ballot_sync(0xffffffffu, pass);
-                if (mk) {
-                    uint32_t pos0 = 0;
-                    if (lane == 0) pos0 = atomicAdd(n_cand, (uint32_t)__popc(mk));
-                    pos0 = __shfl_sync(0xffffffffu, pos0, 0);
-                    if (pass) cand[pos0 + __popc(mk & ((1u << lane) - 1))] = key;
-                }
-            }
-            named_bar_sync(1, kPq2Warps * 32);
-            uint32_t nc = *n_cand;
-            // windows of 2048 keys -> their 128 best at the window start -> packed -> again, until one window is left
-            for (;;) {
-                const uint32_t nw = (nc + 2047) / 2048;
-                for (uint32_t w = 0; w < nw; w++) {
-                    const uint32_t nk = nc - w * 2048 < 2048 ? nc - w * 2048 : 2048;
-                    coop_top128(cand + (size_t)w * 2048, nk, (nk + 127) / 128, warp, lane);
-                }
-                if (nw == 1) break;
-                for (uint32_t i = 128 + threadIdx.x; i < nw * 128; i += kPq2Warps * 32)
-                    cand[i] = cand[(size_t)(i >> 7) * 2048 + (i & 127)];
+            // Rows [i_begin, i_end) are appended if they beat `thr`, then everything staged is reduced to the 128
+            // best.  Without a threshold yet (the CTA's first block) the first 1920 rows go in unfiltered and give
+            // one; the rest of the block is then filtered against it (a few percent pass) in a second round.
+            uint32_t i_begin = 0;
+            while (i_begin < n) {
+                const uint64_t thr = top[p.k - 1];
+                const uint32_t i_end = (thr == 0 && n - i_begin > 1920) ? i_begin + 1920 : n;
+                named_bar_sync(1, kPq2Warps * 32);  // everyone has read top[] / thr
+                if (threadIdx.x < 128) cand[threadIdx.x] = top[threadIdx.x];
+                if (threadIdx.x == 0) *n_cand = 128;
                 named_bar_sync(1, kPq2Warps * 32);
-                nc = nw * 128;
+                for (uint32_t i0 = i_begin; i0 < i_end; i0 += kPq2Warps * 32) {
+                    const uint32_t i = i0 + threadIdx.x;
+                    uint64_t key = 0;
+                    if (i < i_end) key = make_key(acc[i], p.id_base + (uint32_t)(row0 + i), p.flip);
+                    const bool pass = i < i_end && key > thr;
+                    const uint32_t mk = __ballot_sync(0xffffffffu, pass);
+                    if (mk) {
+                        uint32_t pos0 = 0;
+                        if (lane == 0) pos0 = atomicAdd(n_cand, (uint32_t)__popc(mk));
+                        pos0 = __shfl_sync(0xffffffffu, pos0, 0);
+                        if (pass) cand[pos0 + __popc(mk & ((1u << lane) - 1))] = key;
+                    }
+                }
+                named_bar_sync(1, kPq2Warps * 32);
+                uint32_t nc = *n_cand;
+                // windows of 2048 keys -> their 128 best at the window start -> packed -> again, until one is left
+                for (;;) {
+                    const uint32_t nw = (nc + 2047) / 2048;
+                    for (uint32_t w = 0; w < nw; w++) {
+                        const uint32_t nk = nc - w * 2048 < 2048 ? nc - w * 2048 : 2048;
+                        coop_top128(cand + (size_t)w * 2048, nk, (nk + 127) / 128, warp, lane);
+                    }
+                    if (nw == 1) break;
+                    for (uint32_t i = 128 + threadIdx.x; i < nw * 128; i += kPq2Warps * 32)
+                        cand[i] = cand[(size_t)(i >> 7) * 2048 + (i & 127)];
+                    named_bar_sync(1, kPq2Warps * 32);
+                    nc = nw * 128;
+                }
+                if (threadIdx.x < 128) top[threadIdx.x] = cand[threadIdx.x];
+                named_bar_sync(1, kPq2Warps * 32);
+                i_begin = i_end;
             }
-            if (threadIdx.x < 128) top[threadIdx.x] = cand[threadIdx.x];
             // (the barrier at the top of the next slice / after the loop orders this against the next LUT load)
         }
     }
@@ -236,7 +248,8 @@ bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32
         attr_done = true;
     }
     CUtensorMap map;
-    if (!make_tensor_map_u8_2d(&map, d_codes, count, n_chunks, kPq2SliceChunks, kPq2TileRows, CU_TENSOR_MAP_SWIZZLE_NONE))
+    if (!make_tensor_map_u8_2d(&map, d_codes, count, n_chunks, kPq2SliceChunks, kPq2TileRows, CU_TENSOR_MAP_SWIZZLE_NONE,
+                               CU_TENSOR_MAP_L2_PROMOTION_NONE))
         return false;
     PqScan2Params p{};
     p.count = count;
