@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the workload's BASELINE size)")
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="rows of the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: top-k exchange inside the scan launch over peer memory (u8, bin) or all-gather + merge")
     a = ap.parse_args()
     a.steps = a.steps or (20 if a.workload == "u8batch" else 1000)
     a.warmup = a.warmup or (3 if a.workload == "u8batch" else 20)
@@ -237,7 +239,10 @@ def run_gpu(args):
     d_scores = torch.zeros(k, dtype=torch.float32, device=dev)
     d_ids = torch.zeros(k, dtype=torch.int32, device=dev)
     from quantization_b200.sharded import ShardedSearch
-    ss = ShardedSearch(ix, device=dev)  # scan -> all-gather of k keys per rank (NCCL) -> merge, on `stream`
+    # N > 1: scan + exchange of the k keys per rank + merge.  "peer": inside the scan launch over peer memory
+    # (NVLink); "nccl" (and the PQ codec): all-gather on `stream`, then a merge launch
+    use_peer = world > 1 and args.exchange == "peer" and args.workload in ("u8", "bin")
+    ss = ShardedSearch(ix, device=dev, peer=use_peer)
 
     def step_dev():
         nonlocal d_scores, d_ids
@@ -290,10 +295,13 @@ def run_gpu(args):
     # e2e: the host-buffer calls a user of the trait makes, every step: f32 query -> encode_query ->
     # scan_topk -> (scores, ids) on the host
     for _ in range(3):
-        ix.search(q_host, k, True)
+        ss.search(q_host, k, True) if use_peer else ix.search(q_host, k, True)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
+        if use_peer:  # qz_search_topk_peer: the same call, exchange included: global results on every rank
+            hs, hi = ss.search(q_host, k, True)
+            continue
         hs, hi = ix.search(q_host, k, True)  # qz_search_topk: H2D query, encode_query, scan + top-k, D2H results
         if world > 1:  # host-side exchange of the k results per rank, then merge on the device
             mine = torch.from_numpy(np.concatenate([hs.view(np.uint32), hi]).astype(np.int64)).to(dev)
@@ -320,12 +328,16 @@ def run_gpu(args):
             "data": "synthetic: torch.rand embeddings generated and encoded on the device, seed 42 + rank",
             "config": {"workload": wl["name"], "rows_per_gpu": rows, "dim": wl["dim"], "k": k,
                        "bytes_per_vector": wl["row_bytes"], "sharding": f"point-id ranges x{world}",
+                       "exchange": ("none (1 GPU)" if world == 1 else
+                                    "peer memory inside the scan launch (qz_scan_topk_peer_dev)" if use_peer else
+                                    "NCCL all-gather of k keys + merge launch"),
                        "l2": f"input {rows * wl['row_bytes'] / 1e6:.0f} MB per GPU per step "
                              + ("exceeds" if rows * wl["row_bytes"] > 126e6 else "FITS IN") + " the 126 MB L2; no flush"},
             "e2e": {"value": total_rows * args.steps / (e2e_ms * 1e-3), "unit": "vectors/s",
                     "h2d_bytes_per_step": int(q_host.nbytes),
                     "d2h_bytes_per_step": int(k * 8), "ms_per_step": e2e_ms / args.steps,
-                    "call": "qz_search_topk (host f32 query -> host scores, ids), one call per step"},
+                    "call": ("qz_search_topk_peer" if use_peer else "qz_search_topk") +
+                            " (host f32 query -> host scores, ids), one call per step"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(args.workload) if rows == wl["rows"] else None,

@@ -235,6 +235,28 @@ QZ_API qz_status qz_score_pairs(qz_index *index, const uint32_t *rows_a, const u
 QZ_API qz_status qz_merge_topk_dev(qz_ctx *ctx, const uint64_t *d_keys_in, uint32_t n_lists, uint32_t k,
                                    int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
 
+/* ---- multi-GPU: top-k exchange over peer memory, fused into the scan launch -------------------------
+ * One process per GPU, shards = contiguous point-id ranges (id_base = first row).  Replaces, per query,
+ * qz_scan_topk_dev + an all-gather of the k keys + qz_merge_topk_dev with ONE kernel launch per GPU: the scan's
+ * last thread block stores its k best keys into every peer's buffer over NVLink, raises a flag, waits for the
+ * peers' flags and merges.  Every rank must make the same sequence of calls (like a collective).  u8 and binary
+ * indexes, k <= 128, non-empty shards; a peer that never arrives makes the kernel trap after ~30 s.
+ *   qz_peer_create   allocates this GPU's buffer; handle_out = QZ_PEER_HANDLE_BYTES bytes (a CUDA IPC handle)
+ *                    that the caller ships to the other ranks
+ *   qz_peer_connect  all_handles = [world][QZ_PEER_HANDLE_BYTES] in rank order; maps the peers' buffers
+ *   qz_scan_topk_peer_dev  as qz_scan_topk_dev, results = the global top-k on every rank */
+#define QZ_PEER_HANDLE_BYTES 64
+typedef struct qz_peer qz_peer;
+QZ_API qz_status qz_peer_create(qz_ctx *ctx, uint32_t world, uint32_t rank, uint8_t *handle_out, qz_peer **out);
+QZ_API qz_status qz_peer_connect(qz_peer *peer, const uint8_t *all_handles);
+QZ_API void qz_peer_destroy(qz_peer *peer);
+QZ_API qz_status qz_scan_topk_peer_dev(qz_index *index, qz_peer *peer, const void *d_enc_query, uint32_t k,
+                                       int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
+/* host-buffer form (the multi-GPU qz_search_topk): f32 query in, the global top-k out on every rank, one call,
+ * one synchronisation; *n_out = min(k, rows over all shards) */
+QZ_API qz_status qz_search_topk_peer(qz_index *index, qz_peer *peer, const float *query, uint32_t k, int32_t largest,
+                                     float *scores, uint32_t *ids, uint32_t *n_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -68,6 +68,11 @@ _SIGS = {
     "qz_score_points": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
     "qz_score_pairs": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
     "qz_merge_topk_dev": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp, vp]),
+    "qz_peer_create": (C.c_int32, [vp, C.c_uint32, C.c_uint32, vp, C.POINTER(vp)]),
+    "qz_peer_connect": (C.c_int32, [vp, vp]),
+    "qz_peer_destroy": (None, [vp]),
+    "qz_scan_topk_peer_dev": (C.c_int32, [vp, vp, vp, C.c_uint32, C.c_int32, vp, vp, vp]),
+    "qz_search_topk_peer": (C.c_int32, [vp, vp, vp, C.c_uint32, C.c_int32, vp, vp, u32p]),
 }
 
 _lib = None

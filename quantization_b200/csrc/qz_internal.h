@@ -111,6 +111,7 @@ struct ScanFinal {  // where the scan kernel's in-launch final merge writes (eac
     float *d_scores;
     uint32_t *d_ids;
     bool *fused;  // out: the kernel did the final merge
+    const void *px = nullptr;  // optional qz::PeerExchange (row_scan.cuh): cross-GPU exchange in the same launch
 };
 qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, uint32_t k, int largest,
                           uint32_t *n_lists, uint32_t *Kp_out, const ScanFinal *fin = nullptr);

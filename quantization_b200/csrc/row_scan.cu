@@ -141,7 +141,9 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
         const uint32_t lpc = pow2_ceil(grid < 2 ? 2 : grid);
         size_t need = (size_t)(lpc / 2) * Kp * 8;
         if (need < kPruneSmem) need = kPruneSmem;
-        if (need <= (size_t)pl.n_slots * pl.slot_bytes) {
+        // the merge works in the kernel's shared memory from offset 0 (ring, then the by then dead top-k areas)
+        if (need <= ctx->smem_optin) {
+            if (pl.smem < need) pl.smem = need;
             MergeParams &m = p.merge;
             m.in = ctx->d_partial;
             m.n_lists = grid;
@@ -158,8 +160,16 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
             m.ids = fin->d_ids;
             p.done = ctx->d_done;
             *fin->fused = true;
+            if (fin->px) {
+                p.px = *static_cast<const PeerExchange *>(fin->px);
+                m.keys = p.px.gather[p.px.rank] + ((size_t)p.px.buf * p.px.world + p.px.rank) * kPeerStride;
+                m.scores = nullptr;
+                m.ids = nullptr;
+            }
         }
     }
+    if (fin && fin->px && !*fin->fused)
+        return fail(ctx, QZ_ARGUMENTS, "peer exchange needs the in-launch merge (k <= 128, streaming row shape)");
     cudaError_t e;
     timing_begin(ctx);
     if (ix->codec == QZ_CODEC_BIN && pl.vec) e = launch_row_scan_xorv(pl.lpr, pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);

@@ -55,7 +55,9 @@ def results_to_keys(scores, ids, largest):
 class ShardedSearch:
     """search_top_k over all ranks' shards; every rank returns the same (scores, ids)."""
 
-    def __init__(self, index=None, group=None, device=None, *, local_topk=None, merge=None):
+    def __init__(self, index=None, group=None, device=None, *, local_topk=None, merge=None, peer=False):
+        """peer=True: exchange through peer memory inside the scan launch (qz_scan_topk_peer_dev: one kernel per
+        query per GPU, no collective call) instead of all-gather + merge.  u8 / binary indexes, k <= 128."""
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -67,6 +69,9 @@ class ShardedSearch:
         self._local_topk = local_topk if local_topk is not None else self._gpu_local_topk
         self._merge = merge if merge is not None else self._gpu_merge
         self._bufs = {}
+        self._peer = None
+        if peer and self.world > 1:
+            self._peer_setup()
 
     # ---- device steps (the product path) -----------------------------------------------------------
     def _buffers(self, k):
@@ -86,10 +91,39 @@ class ShardedSearch:
         ctx.check(ctx._L.qz_merge_topk_dev(ctx.handle, C.c_void_p(d_all.data_ptr()), n_lists, k, int(bool(largest)),
                                            None, C.c_void_p(d_scores.data_ptr()), C.c_void_p(d_ids.data_ptr())))
 
+    # ---- peer-memory exchange (csrc/peer.cu) ----------------------------------------------------------
+    PEER_HANDLE_BYTES = 64
+
+    def _peer_setup(self):
+        """create this rank's symmetric buffer, all-gather the CUDA IPC handles, map the peers"""
+        t, ctx = self.torch, self.index.ctx
+        mine = np.zeros(self.PEER_HANDLE_BYTES, np.uint8)
+        h = C.c_void_p()
+        ctx.check(ctx._L.qz_peer_create(ctx.handle, self.world, self.rank, C.c_void_p(mine.ctypes.data), C.byref(h)))
+        d_mine = t.from_numpy(mine).to(self.device)
+        d_all = t.zeros(self.world * self.PEER_HANDLE_BYTES, dtype=t.uint8, device=self.device)
+        self.dist.all_gather_into_tensor(d_all, d_mine, group=self.group)
+        handles = np.ascontiguousarray(d_all.cpu().numpy())
+        ctx.check(ctx._L.qz_peer_connect(h, C.c_void_p(handles.ctypes.data)))
+        self.dist.barrier(group=self.group)  # every rank has mapped every buffer before the first scan
+        self._peer = h
+
+    def close(self):
+        if self._peer is not None:
+            self.dist.barrier(group=self.group)  # no peer may still be writing into this rank's buffer
+            self.index.ctx._L.qz_peer_destroy(self._peer)
+            self._peer = None
+
     # ---- the step ------------------------------------------------------------------------------------
     def search_top_k_dev(self, d_query, k, largest=True):
         """asynchronous on the current stream; returns device tensors (scores[k], ids[k]) valid on every rank"""
         d_keys, d_all, d_scores, d_ids = self._buffers(k)
+        if self._peer is not None:
+            ctx = self.index.ctx
+            ctx.check(ctx._L.qz_scan_topk_peer_dev(self.index.handle, self._peer, C.c_void_p(d_query), k,
+                                                   int(bool(largest)), None, C.c_void_p(d_scores.data_ptr()),
+                                                   C.c_void_p(d_ids.data_ptr())))
+            return d_scores, d_ids
         self._local_topk(d_query, k, largest, d_keys)
         if self.world > 1:
             self.dist.all_gather_into_tensor(d_all, d_keys, group=self.group)
@@ -97,6 +131,19 @@ class ShardedSearch:
             d_all.copy_(d_keys)
         self._merge(d_all, self.world, k, largest, d_scores, d_ids)
         return d_scores, d_ids
+
+    def search(self, query_f32, k, largest=True):
+        """host f32 query -> the global (scores, ids) on every rank: encode_query, scan, exchange and the copies
+        in one library call (peer mode only)"""
+        if self._peer is None:
+            raise RuntimeError("ShardedSearch.search needs peer=True and world > 1")
+        ctx = self.index.ctx
+        q = np.ascontiguousarray(query_f32, np.float32).reshape(-1)
+        scores, ids, n = np.empty(k, np.float32), np.empty(k, np.uint32), C.c_uint32(0)
+        ctx.check(ctx._L.qz_search_topk_peer(self.index.handle, self._peer, C.c_void_p(q.ctypes.data), k,
+                                             int(bool(largest)), C.c_void_p(scores.ctypes.data),
+                                             C.c_void_p(ids.ctypes.data), C.byref(n)))
+        return scores[: n.value], ids[: n.value]
 
     def search_top_k(self, d_query, k, largest=True, total_count=None):
         s, i = self.search_top_k_dev(d_query, k, largest)
