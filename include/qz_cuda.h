@@ -228,6 +228,13 @@ QZ_API qz_status qz_score_points(qz_index *index, const void *enc_query, const u
  * (u8.rs:386-453, binary.rs:302-314, pq.rs:566-593) */
 QZ_API qz_status qz_score_pairs(qz_index *index, const uint32_t *rows_a, const uint32_t *rows_b, uint64_t n,
                                 float *scores);
+/* device-pointer forms for callers that keep candidate lists on the device (graph search: the id-list scoring of
+ * demos/benches/encode.rs:91-102, binary.rs:62-72, pq.rs:41-46): asynchronous on the context stream, ids are not
+ * range-checked */
+QZ_API qz_status qz_score_points_dev(qz_index *index, const void *d_enc_query, const uint32_t *d_rows, uint64_t n,
+                                     float *d_scores);
+QZ_API qz_status qz_score_pairs_dev(qz_index *index, const uint32_t *d_rows_a, const uint32_t *d_rows_b, uint64_t n,
+                                    float *d_scores);
 
 /* Merge `n_lists` best-first top-k lists (e.g. one per shard after an all-gather) into one.
  * Device pointers, asynchronous: d_keys_in = [n_lists][k] u64 keys as produced by

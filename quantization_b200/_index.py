@@ -86,6 +86,14 @@ class DeviceIndex:
         self.ctx.check(self._L.qz_scan_topk_dev(self.handle, C.c_void_p(d_query), k, int(bool(largest)),
                                                 C.c_void_p(d_keys), C.c_void_p(d_scores), C.c_void_p(d_ids)))
 
+    def score_points_dev(self, d_query, d_rows, n, d_scores):
+        self.ctx.check(self._L.qz_score_points_dev(self.handle, C.c_void_p(d_query), C.c_void_p(d_rows), n,
+                                                   C.c_void_p(d_scores)))
+
+    def score_pairs_dev(self, d_rows_a, d_rows_b, n, d_scores):
+        self.ctx.check(self._L.qz_score_pairs_dev(self.handle, C.c_void_p(d_rows_a), C.c_void_p(d_rows_b), n,
+                                                  C.c_void_p(d_scores)))
+
     def score_all_dev(self, d_query, d_scores):
         self.ctx.check(self._L.qz_scan_scores_dev(self.handle, C.c_void_p(d_query), C.c_void_p(d_scores)))
 

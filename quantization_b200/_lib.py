@@ -67,6 +67,8 @@ _SIGS = {
     "qz_scan_scores_dev": (C.c_int32, [vp, vp, vp]),
     "qz_score_points": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
     "qz_score_pairs": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
+    "qz_score_points_dev": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
+    "qz_score_pairs_dev": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
     "qz_merge_topk_dev": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp, vp]),
     "qz_peer_create": (C.c_int32, [vp, C.c_uint32, C.c_uint32, vp, C.POINTER(vp)]),
     "qz_peer_connect": (C.c_int32, [vp, vp]),

@@ -350,6 +350,28 @@ qz_status qz_score_pairs(qz_index *ix, const uint32_t *rows_a, const uint32_t *r
     return score_ids_common(ix, nullptr, rows_a, rows_b, n, scores, true);
 }
 
+// device-pointer forms: ids, query and outputs already on the device, asynchronous, ids are NOT range-checked
+qz_status qz_score_points_dev(qz_index *ix, const void *d_enc_query, const uint32_t *d_rows, uint64_t n,
+                              float *d_scores) {
+    if (bad_index(ix)) return QZ_ARGUMENTS;
+    if (n == 0) return QZ_OK;
+    if (!d_rows || !d_scores || (!d_enc_query && qz_query_bytes(ix)))
+        return fail(ix->ctx, QZ_ARGUMENTS, "score_points_dev: NULL argument");
+    QZ_CUDA(ix->ctx, cudaSetDevice(ix->ctx->device));
+    if (ix->codec == QZ_CODEC_PQ) return pq_score_points(ix, d_enc_query, d_rows, n, d_scores);
+    return launch_gather(ix, d_enc_query, nullptr, d_rows, n, d_scores);
+}
+
+qz_status qz_score_pairs_dev(qz_index *ix, const uint32_t *d_rows_a, const uint32_t *d_rows_b, uint64_t n,
+                             float *d_scores) {
+    if (bad_index(ix)) return QZ_ARGUMENTS;
+    if (n == 0) return QZ_OK;
+    if (!d_rows_a || !d_rows_b || !d_scores) return fail(ix->ctx, QZ_ARGUMENTS, "score_pairs_dev: NULL argument");
+    QZ_CUDA(ix->ctx, cudaSetDevice(ix->ctx->device));
+    if (ix->codec == QZ_CODEC_PQ) return pq_score_pairs(ix, d_rows_a, d_rows_b, n, d_scores);
+    return launch_gather(ix, nullptr, d_rows_a, d_rows_b, n, d_scores);
+}
+
 }  // extern "C"
 
 extern "C" {
