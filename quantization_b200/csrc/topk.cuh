@@ -136,10 +136,13 @@ __device__ __forceinline__ void reg128_merge_desc(uint64_t (&v)[4], int lane) {
 // keys[n_keys .. n_chunks*128) is zero-filled here.  Chunk w is sorted by warp w in registers, then
 // a pairwise max-merge tree (log2(n_chunks) levels) runs with one warp per surviving pair.
 constexpr int kCoopWarps = 16;
-__device__ __forceinline__ void coop_top128(uint64_t *keys, uint32_t n_keys, uint32_t n_chunks, uint32_t warp,
-                                            uint32_t lane) {
-    for (uint32_t i = n_keys + warp * 32 + lane; i < n_chunks * 128; i += kCoopWarps * 32) keys[i] = 0ull;
-    asm volatile("bar.sync 1, %0;" ::"r"(kCoopWarps * 32) : "memory");
+// NW = warps taking part (all of them call; they must be warps 0..NW-1 of the CTA and the only users of named
+// barrier 1); n_chunks <= NW.
+template <int NW>
+__device__ __forceinline__ void coop_top128_t(uint64_t *keys, uint32_t n_keys, uint32_t n_chunks, uint32_t warp,
+                                              uint32_t lane) {
+    for (uint32_t i = n_keys + warp * 32 + lane; i < n_chunks * 128; i += NW * 32) keys[i] = 0ull;
+    asm volatile("bar.sync 1, %0;" ::"r"(NW * 32) : "memory");
     if (warp < n_chunks) {
         uint64_t c[4];
         uint64_t *ch = keys + warp * 128;
@@ -150,7 +153,7 @@ __device__ __forceinline__ void coop_top128(uint64_t *keys, uint32_t n_keys, uin
         for (int r = 0; r < 4; r++) ch[lane * 4 + r] = c[r];
     }
     for (uint32_t stride = 1; stride < n_chunks; stride <<= 1) {
-        asm volatile("bar.sync 1, %0;" ::"r"(kCoopWarps * 32) : "memory");
+        asm volatile("bar.sync 1, %0;" ::"r"(NW * 32) : "memory");
         if ((warp & (2 * stride - 1)) == 0 && warp + stride < n_chunks) {
             uint64_t *A = keys + warp * 128, *B = keys + (warp + stride) * 128;
             uint64_t t[4];
@@ -164,7 +167,11 @@ __device__ __forceinline__ void coop_top128(uint64_t *keys, uint32_t n_keys, uin
             for (int r = 0; r < 4; r++) A[lane * 4 + r] = t[r];
         }
     }
-    asm volatile("bar.sync 1, %0;" ::"r"(kCoopWarps * 32) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"r"(NW * 32) : "memory");
+}
+__device__ __forceinline__ void coop_top128(uint64_t *keys, uint32_t n_keys, uint32_t n_chunks, uint32_t warp,
+                                            uint32_t lane) {
+    coop_top128_t<kCoopWarps>(keys, n_keys, n_chunks, warp, lane);
 }
 
 // Merge one warp's staged candidates cand[0..cnt) into the CTA list.  Called by a full warp.
