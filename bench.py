@@ -52,7 +52,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="rows of the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                    help="N > 1: top-k exchange inside the scan launch over peer memory (u8, bin) or all-gather + merge")
+                    help="N > 1: top-k exchange inside the scan launch over peer memory, or NCCL all-gather + merge launch")
     a = ap.parse_args()
     a.steps = a.steps or (20 if a.workload == "u8batch" else 1000)
     a.warmup = a.warmup or (3 if a.workload == "u8batch" else 20)
@@ -240,8 +240,8 @@ def run_gpu(args):
     d_ids = torch.zeros(k, dtype=torch.int32, device=dev)
     from quantization_b200.sharded import ShardedSearch
     # N > 1: scan + exchange of the k keys per rank + merge.  "peer": inside the scan launch over peer memory
-    # (NVLink); "nccl" (and the PQ codec): all-gather on `stream`, then a merge launch
-    use_peer = world > 1 and args.exchange == "peer" and args.workload in ("u8", "bin")
+    # (NVLink); "nccl": all-gather on `stream`, then a merge launch
+    use_peer = world > 1 and args.exchange == "peer"
     ss = ShardedSearch(ix, device=dev, peer=use_peer)
 
     def step_dev():

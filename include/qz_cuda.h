@@ -246,8 +246,8 @@ QZ_API qz_status qz_merge_topk_dev(qz_ctx *ctx, const uint64_t *d_keys_in, uint3
  * One process per GPU, shards = contiguous point-id ranges (id_base = first row).  Replaces, per query,
  * qz_scan_topk_dev + an all-gather of the k keys + qz_merge_topk_dev with ONE kernel launch per GPU: the scan's
  * last thread block stores its k best keys into every peer's buffer over NVLink, raises a flag, waits for the
- * peers' flags and merges.  Every rank must make the same sequence of calls (like a collective).  u8 and binary
- * indexes, k <= 128, non-empty shards; a peer that never arrives makes the kernel trap after ~30 s.
+ * peers' flags and merges.  Every rank must make the same sequence of calls (like a collective).  Any codec (PQ:
+ * row pitch a multiple of 16 bytes), k <= 128, non-empty shards; a peer that never arrives makes the kernel trap after ~30 s.
  *   qz_peer_create   allocates this GPU's buffer; handle_out = QZ_PEER_HANDLE_BYTES bytes (a CUDA IPC handle)
  *                    that the caller ships to the other ranks
  *   qz_peer_connect  all_handles = [world][QZ_PEER_HANDLE_BYTES] in rank order; maps the peers' buffers

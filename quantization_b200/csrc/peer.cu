@@ -23,6 +23,11 @@ static size_t gather_bytes(uint32_t world) { return (size_t)2 * world * kPeerStr
 static size_t peer_bytes(uint32_t world) { return gather_bytes(world) + 256; }
 }  // namespace qz
 
+namespace qz {
+qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, int largest, uint32_t *n_lists,
+                  uint32_t *Kp_out, const ScanFinal *fin);
+}
+
 using namespace qz;
 
 extern "C" {
@@ -92,7 +97,6 @@ qz_status qz_scan_topk_peer_dev(qz_index *ix, qz_peer *pe, const void *d_enc_que
     if (pe->ctx != ctx) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: index and peer group live on different contexts");
     if (!pe->connected && pe->world > 1) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: qz_peer_connect first");
     if (k == 0 || k > kPeerStride) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: k must be in [1, 128]");
-    if (ix->codec == QZ_CODEC_PQ) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: u8 and binary indexes only");
     if (ix->count == 0) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: empty shard");
     if (!d_enc_query) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: NULL query");
     if (pe->world == 1) return qz_scan_topk_dev(ix, d_enc_query, k, largest, d_keys, d_scores, d_ids);
@@ -123,8 +127,14 @@ qz_status qz_scan_topk_peer_dev(qz_index *ix, qz_peer *pe, const void *d_enc_que
     bool fused = false;
     ScanFinal fin{nullptr, nullptr, nullptr, &fused, &x};
     uint32_t n_lists = 0, Kp = 0;
-    qz_status st = launch_row_scan(ix, d_enc_query, nullptr, k, largest, &n_lists, &Kp, &fin);
-    if (st != QZ_OK) pe->seq--;  // nothing was launched: the step did not happen
+    qz_status st;
+    if (ix->codec == QZ_CODEC_PQ) {
+        st = pq_scan(ix, d_enc_query, nullptr, k, largest, &n_lists, &Kp, &fin);
+        if (st == QZ_OK && !fused) st = fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: PQ row pitch must be a multiple of 16 bytes");
+    } else {
+        st = launch_row_scan(ix, d_enc_query, nullptr, k, largest, &n_lists, &Kp, &fin);
+    }
+    if (st != QZ_OK) pe->seq--;  // the exchange did not happen
     return st;
 }
 

@@ -20,7 +20,7 @@ namespace qz {
 
 bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32_t n_chunks, uint32_t n_slices,
                      const float *d_perm, float *d_scores, uint32_t k, int largest, uint32_t id_base, uint32_t *n_lists,
-                     cudaError_t *err);
+                     const ScanFinal *fin, cudaError_t *err);
 
 constexpr int kPqCentroids = 256;     // CENTROIDS_COUNT, pq.rs:25
 constexpr int kSliceChunks = 128;     // chunks per LUT slice: 32 lanes x 4 code bytes
@@ -210,7 +210,8 @@ qz_status pq_encode_query(qz_index *ix, const float *d_queries, uint32_t nq, voi
 }
 
 qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, int largest, uint32_t *n_lists,
-                  uint32_t *Kp_out) {
+                  uint32_t *Kp_out, const ScanFinal *fin) {
+    if (fin) *fin->fused = false;
     qz_ctx *ctx = ix->ctx;
     static bool attr_done = false;
     if (!attr_done) {
@@ -237,7 +238,7 @@ qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, 
         cudaError_t e2 = cudaSuccess;
         uint32_t lists = 0;
         if (pq_scan2_launch(ctx, ix->d_storage, ix->count, ix->n_chunks, slices, ix->d_lut_perm, sc, fused ? k : 0, largest,
-                            ix->id_base, &lists, &e2)) {
+                            ix->id_base, &lists, fused ? fin : nullptr, &e2)) {
             if (e2 != cudaSuccess) return cuda_fail(ctx, e2, "pq_scan2_kernel");
             ctx->launches++;
             if (fused) {

@@ -21,6 +21,7 @@
 #include "common.cuh"
 #include "qz_internal.h"
 #include "topk.cuh"
+#include "peer_exchange.cuh"
 #include "tensor_map.h"
 
 namespace qz {
@@ -42,6 +43,10 @@ struct PqScan2Params {
     float *scores;      // optional [count]
     uint64_t *partial;  // optional [gridDim.x][128]: the CTA's 128 best keys, best first (fused top-k, k <= 128)
     uint32_t k, flip, id_base;
+    // in-launch final merge + optional cross-GPU exchange, as in row_scan.cuh (done != NULL: last CTA merges)
+    uint32_t *done;
+    MergeParams merge;
+    PeerExchange px;
 };
 
 __device__ __forceinline__ void pq2_tma_tile(void *dst, const CUtensorMap *map, int32_t c0, int32_t c1, uint64_t *bar) {
@@ -230,6 +235,21 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
     if (do_topk) {
         named_bar_sync(1, kPq2Warps * 32);
         if (threadIdx.x < 128) p.partial[(size_t)blockIdx.x * 128 + threadIdx.x] = top[threadIdx.x];
+        if (p.done) {
+            __threadfence();
+            named_bar_sync(1, kPq2Warps * 32);
+            if (threadIdx.x == 0) {
+                const uint32_t prev = atomicAdd(p.done, 1u);
+                __threadfence();
+                *n_cand = prev == gridDim.x - 1;
+            }
+            named_bar_sync(1, kPq2Warps * 32);
+            if (*n_cand) {  // last CTA: all lists are published; the LUT area is the merge's work area
+                prune_merge<1, true>(p.merge, reinterpret_cast<uint64_t *>(slut), threadIdx.x, kPq2Warps * 32);
+                if (threadIdx.x == 0) *p.done = 0;
+                if (p.px.world > 1) peer_exchange_merge(p.px, p.k, reinterpret_cast<uint64_t *>(slut));
+            }
+        }
     }
 }
 
@@ -238,7 +258,7 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
 // k == 0: scores only.  0 < k <= 128: the per-CTA lists go to ctx->d_partial ([*n_lists][128]) and d_scores is optional.
 bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32_t n_chunks, uint32_t n_slices,
                      const float *d_perm, float *d_scores, uint32_t k, int largest, uint32_t id_base, uint32_t *n_lists,
-                     cudaError_t *err) {
+                     const ScanFinal *fin, cudaError_t *err) {
     *err = cudaSuccess;
     if (n_chunks % 16 != 0 || count == 0 || count > 0x7FFFFFFFull) return false;
     static bool attr_done = false;
@@ -279,6 +299,31 @@ bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32
     p.n_blocks = (uint32_t)((count + p.block_rows - 1) / p.block_rows);
     const uint32_t grid = p.n_blocks < (uint32_t)ctx->sm_count ? p.n_blocks : (uint32_t)ctx->sm_count;
     const size_t smem = fixed + (size_t)p.block_rows * 4;
+    if (fin) *fin->fused = false;
+    if (fin && k && grid <= kPruneMaxLists && !getenv("QZ_SCAN_NO_FUSED_MERGE")) {
+        MergeParams &m = p.merge;
+        m.in = ctx->d_partial;
+        m.n_lists = grid;
+        m.in_len = 128;
+        m.in_stride = 128;
+        m.Kp = 128;
+        m.lists_per_cta = pow2_ceil(grid < 2 ? 2 : grid);
+        m.out = nullptr;
+        m.final_out = 1;
+        m.k = k;
+        m.flip = p.flip;
+        m.keys = fin->d_keys;
+        m.scores = fin->d_scores;
+        m.ids = fin->d_ids;
+        p.done = ctx->d_done;
+        *fin->fused = true;
+        if (fin->px) {
+            p.px = *static_cast<const PeerExchange *>(fin->px);
+            m.keys = p.px.gather[p.px.rank] + ((size_t)p.px.buf * p.px.world + p.px.rank) * kPeerStride;
+            m.scores = nullptr;
+            m.ids = nullptr;
+        }
+    }
     timing_begin(ctx);
     pq_scan2_kernel<<<grid, kPq2Threads, smem, ctx->stream>>>(map, p);
     timing_end(ctx);

@@ -8,7 +8,7 @@ using namespace qz;
 namespace qz {
 // pq.cu
 qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, int largest, uint32_t *n_lists,
-                  uint32_t *Kp_out);
+                  uint32_t *Kp_out, const ScanFinal *fin);
 qz_status pq_encode_query(qz_index *ix, const float *d_queries, uint32_t nq, void *d_out);
 qz_status pq_score_points(qz_index *ix, const void *d_lut, const uint32_t *d_rows, uint64_t n, float *d_out);
 qz_status pq_score_pairs(qz_index *ix, const uint32_t *d_a, const uint32_t *d_b, uint64_t n, float *d_out);
@@ -39,7 +39,7 @@ qz_status index_alloc_storage(qz_index *ix, const uint8_t *host_storage) {
 static qz_status scan_any(qz_index *ix, const void *d_query, float *d_scores, uint32_t k, int largest,
                           uint32_t *n_lists, uint32_t *Kp, const ScanFinal *fin = nullptr) {
     qz_ctx *ctx = ix->ctx;
-    if (ix->codec == QZ_CODEC_PQ) return pq_scan(ix, d_query, d_scores, k, largest, n_lists, Kp);
+    if (ix->codec == QZ_CODEC_PQ) return pq_scan(ix, d_query, d_scores, k, largest, n_lists, Kp, fin);
     qz_status st = launch_row_scan(ix, d_query, d_scores, k, largest, n_lists, Kp, fin);
     if (st != QZ_ARGUMENTS) return st;
     // row shape outside the streaming kernel (rows that are not whole words, or huge rows):

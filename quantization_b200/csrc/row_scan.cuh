@@ -22,6 +22,7 @@
 #pragma once
 #include "common.cuh"
 #include "topk.cuh"
+#include "peer_exchange.cuh"
 
 namespace qz {
 
@@ -36,31 +37,6 @@ constexpr int kScanThreads = (kConsumerWarps + 1) * 32;
 constexpr int kMaxSlots = 16;
 constexpr int kBatchRows = 8;    // rows one warp scores per step
 constexpr int kTileRowAlign = 16;  // tiles are 16-row multiples => every tile starts 16-byte aligned
-
-// Cross-GPU exchange fused into the scan launch (one process per GPU, shards = point-id ranges).  Every GPU owns a
-// symmetric buffer mapped into its peers (CUDA IPC over NVLink): gather[2][world][128] u64 keys and flags[2][world]
-// u32.  After the in-launch merge the last CTA stores its k best keys into slot [buf][rank] of EVERY GPU's buffer,
-// fences system-wide, raises flag [buf][rank] = seq on every GPU, waits until its own flags [buf][*] all read seq, and
-// merges the world's lists: all ranks end the launch with the same global top-k, with no host-side collective.
-// buf = seq & 1: a rank can be at most one step ahead of a peer (it needs the peer's flag of the step), so two
-// buffers are enough.
-constexpr int kMaxPeers = 8;
-constexpr uint32_t kPeerStride = 128;  // keys per gather slot
-struct PeerExchange {
-    uint32_t world, rank, seq, buf;
-    uint64_t *gather[kMaxPeers];  // gather[g] = base of GPU g's buffer (own = local pointer)
-    uint32_t *flags[kMaxPeers];
-    MergeParams merge;  // world lists of k keys from the local buffer -> final outputs
-};
-
-__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
 
 struct RowScanParams {
     const uint8_t *storage;  // 16-byte aligned, readable up to round_up(count*row_bytes, 16)
@@ -386,30 +362,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             if (*lock) {
                 prune_merge<1, true>(p.merge, reinterpret_cast<uint64_t *>(ring), threadIdx.x, kConsumerWarps * 32);
                 if (threadIdx.x == 0) *p.done = 0;
-                if (p.px.world > 1) {
-                    const PeerExchange &x = p.px;
-                    const size_t slot = ((size_t)x.buf * x.world + x.rank) * kPeerStride;
-                    __threadfence();
-                    named_bar_sync(1, kConsumerWarps * 32);
-                    // publish: this GPU's k keys (just written to its own slot) to the same slot on every peer
-                    for (uint32_t i = threadIdx.x; i < x.world * p.k; i += kConsumerWarps * 32) {
-                        const uint32_t g = i / p.k, j = i - g * p.k;
-                        if (g != x.rank) x.gather[g][slot + j] = __ldcg(reinterpret_cast<const unsigned long long *>(x.gather[x.rank] + slot + j));
-                    }
-                    __threadfence_system();
-                    named_bar_sync(1, kConsumerWarps * 32);
-                    if (threadIdx.x < x.world) {
-                        st_release_sys(x.flags[threadIdx.x] + x.buf * x.world + x.rank, x.seq);
-                        // wait for peer `threadIdx.x`'s keys to have landed here (bounded: a missing peer traps)
-                        const uint32_t *f = x.flags[x.rank] + x.buf * x.world + threadIdx.x;
-                        uint32_t spins = 0;
-                        while (ld_acquire_sys(f) != x.seq) {
-                            if (++spins > (1u << 27)) __trap();
-                        }
-                    }
-                    named_bar_sync(1, kConsumerWarps * 32);
-                    prune_merge<1, true>(x.merge, reinterpret_cast<uint64_t *>(ring), threadIdx.x, kConsumerWarps * 32);
-                }
+                if (p.px.world > 1) peer_exchange_merge(p.px, p.k, reinterpret_cast<uint64_t *>(ring));
             }
         }
     }

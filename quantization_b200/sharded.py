@@ -57,7 +57,7 @@ class ShardedSearch:
 
     def __init__(self, index=None, group=None, device=None, *, local_topk=None, merge=None, peer=False):
         """peer=True: exchange through peer memory inside the scan launch (qz_scan_topk_peer_dev: one kernel per
-        query per GPU, no collective call) instead of all-gather + merge.  u8 / binary indexes, k <= 128."""
+        query per GPU, no collective call) instead of all-gather + merge.  k <= 128."""
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist

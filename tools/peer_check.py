@@ -27,7 +27,7 @@ def main():
     torch.cuda.set_stream(stream)
     ctx = qz.Context(local, stream=stream.cuda_stream)
     ok = True
-    for codec, count, dim in (("u8", 300_007, 256), ("bin", 500_003, 1536), ("u8", 1000, 64)):
+    for codec, count, dim in (("u8", 300_007, 256), ("bin", 500_003, 1536), ("u8", 1000, 64), ("pq", 200_003, 512)):
         rng = np.random.default_rng(5)
         data = rng.random((count, dim), dtype=np.float32) - (0.5 if codec == "bin" else 0.0)
         vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
@@ -37,6 +37,14 @@ def main():
             part, n, base = shard_storage(np.asarray(full.encoded_vectors), row, count, rank, world)
             vps = qz.VectorParameters(dim, n, qz.DistanceType.Dot, False)
             shard = qz.EncodedVectorsU8(ctx, part, vps, full.alpha, full.offset, full.multiplier, id_base=base)
+        elif codec == "pq":
+            n_chunks = dim // 2
+            codes = rng.integers(0, 256, size=(count, n_chunks), dtype=np.uint8)
+            cen = rng.random((256, dim), dtype=np.float32)
+            full = qz.EncodedVectorsPQ(ctx, codes.reshape(-1), vp, 2, cen)
+            part, n, base = shard_storage(codes.reshape(-1), n_chunks, count, rank, world)
+            vps = qz.VectorParameters(dim, n, qz.DistanceType.Dot, False)
+            shard = qz.EncodedVectorsPQ(ctx, part, vps, 2, cen, id_base=base)
         else:
             full = qz.EncodedVectorsBin.encode(data, qz.VecStorageBuilder(), vp, ctx=ctx)
             row = full.row_bytes
