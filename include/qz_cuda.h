@@ -242,6 +242,18 @@ QZ_API qz_status qz_score_pairs_dev(qz_index *index, const uint32_t *d_rows_a, c
 QZ_API qz_status qz_merge_topk_dev(qz_ctx *ctx, const uint64_t *d_keys_in, uint32_t n_lists, uint32_t k,
                                    int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
 
+/* ---- out-of-core scan ---------------------------------------------------------------------------
+ * The encoded storage stays in host memory (any EncodedStorage backend that can hand out contiguous runs of rows,
+ * encoded_storage.rs:7-25; corpora larger than HBM) and is streamed through two device buffers: `buf_a` / `buf_b`
+ * are two indexes of the same codec and parameters created with storage = NULL and count = the chunk capacity in
+ * rows.  Copies (a second stream) overlap the scans; results are those of one resident index over all `count`
+ * rows, ids global.  PCIe-bound; pin the storage (qz_host_pin) for full speed.  enc_query: host blob. */
+QZ_API qz_status qz_host_pin(qz_ctx *ctx, const void *ptr, uint64_t bytes);
+QZ_API qz_status qz_host_unpin(qz_ctx *ctx, const void *ptr);
+QZ_API qz_status qz_scan_topk_chunked(qz_index *buf_a, qz_index *buf_b, const uint8_t *host_storage, uint64_t count,
+                                      const void *enc_query, uint32_t k, int32_t largest, float *scores,
+                                      uint32_t *ids, uint32_t *n_out);
+
 /* ---- multi-GPU: top-k exchange over peer memory, fused into the scan launch -------------------------
  * One process per GPU, shards = contiguous point-id ranges (id_base = first row).  Replaces, per query,
  * qz_scan_topk_dev + an all-gather of the k keys + qz_merge_topk_dev with ONE kernel launch per GPU: the scan's

@@ -81,6 +81,16 @@ class DeviceIndex:
                                               C.byref(n)))
         return scores[: n.value], ids[: n.value]
 
+    def search_top_k_chunked(self, other, host_storage, count, query, k, largest=True):
+        """out-of-core scan (qz_scan_topk_chunked): `self` and `other` are two buffer indexes of the same shape
+        (storage None, count = chunk capacity); host_storage = the flat encoded bytes of `count` rows"""
+        st = np.ascontiguousarray(host_storage, np.uint8)
+        q = np.ascontiguousarray(query, np.uint8)
+        scores, ids, n = np.empty(k, np.float32), np.empty(k, np.uint32), C.c_uint32(0)
+        self.ctx.check(self._L.qz_scan_topk_chunked(self.handle, other.handle, ptr(st), count, ptr(q), k,
+                                                    int(bool(largest)), ptr(scores), ptr(ids), C.byref(n)))
+        return scores[: n.value].copy(), ids[: n.value].copy()
+
     # ---- device-pointer forms (asynchronous on the context stream) -------------------------
     def search_top_k_dev(self, d_query, k, largest, d_keys=0, d_scores=0, d_ids=0):
         self.ctx.check(self._L.qz_scan_topk_dev(self.handle, C.c_void_p(d_query), k, int(bool(largest)),
