@@ -34,8 +34,17 @@ def needs_build():
     return any(os.path.getmtime(p) > t for p in _deps())
 
 
-def _compile(src):
+def _headers_mtime():
+    hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if not f.endswith(".cu")]
+    hs.append(os.path.join(HERE, "..", "include", "qz_cuda.h"))
+    return max(os.path.getmtime(h) for h in hs)
+
+
+def _compile(src, force=False):
     obj = os.path.join(OBJ, src.replace(".cu", ".o"))
+    # incremental: an object newer than its source and every header is reused
+    if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(os.path.join(CSRC, src)), _headers_mtime()):
+        return obj
     r = subprocess.run([NVCC, *FLAGS, "-c", os.path.join(CSRC, src), "-o", obj], capture_output=True, text=True)
     with open(obj + ".log", "w") as f:
         f.write(r.stdout + r.stderr)
@@ -49,7 +58,7 @@ def build(force=False, verbose=False):
         return LIB
     os.makedirs(OBJ, exist_ok=True)
     with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
-        objs = list(ex.map(_compile, SOURCES))
+        objs = list(ex.map(lambda f: _compile(f, force), SOURCES))
     r = subprocess.run([NVCC, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
                         "-cudart", "shared", "-Xlinker", "-rpath,/usr/local/cuda/lib64"], capture_output=True, text=True)
     if r.returncode != 0:

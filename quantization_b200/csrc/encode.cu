@@ -37,9 +37,55 @@ __global__ void __launch_bounds__(256) bin_encode_kernel(const float *data, uint
     }
 }
 
+// Fast path for rows of whole float4s and whole 32-bit output words (every BASELINE shape): one warp per row,
+// lane l reads the float4 at floats [128 j + 4 l, +4) of 128-float segment j (all loads of a 4-segment batch
+// are issued before the first use), turns it into a nibble, and three xor-shuffles gather the eight nibbles of
+// a 32-bit word; lanes 0, 8, 16, 24 store words 4 j + l / 8.  No per-element index arithmetic (the generic
+// kernel above spends its time in a 64-bit division per loaded float).
+__global__ void __launch_bounds__(256) bin_encode_v4_kernel(const float *data, uint64_t count, uint32_t dim,
+                                                            uint32_t row_bytes, uint8_t *out) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t nwarps = (uint64_t)gridDim.x * (blockDim.x >> 5);
+    const uint32_t segs = (row_bytes + 15) / 16;
+    const uint32_t sh = 4 * (lane & 7);
+    for (uint64_t row = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < count; row += nwarps) {
+        const float *v = data + row * dim;
+        uint8_t *o = out + row * row_bytes;
+        for (uint32_t j0 = 0; j0 < segs; j0 += 4) {
+            float4 f[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t i = (j0 + u) * 128 + 4 * lane;
+                f[u] = i < dim ? __ldcs(reinterpret_cast<const float4 *>(v + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                uint32_t w = ((f[u].x > 0.0f ? 1u : 0u) | (f[u].y > 0.0f ? 2u : 0u) | (f[u].z > 0.0f ? 4u : 0u) |
+                              (f[u].w > 0.0f ? 8u : 0u)) << sh;
+                w |= __shfl_xor_sync(0xffffffffu, w, 1);
+                w |= __shfl_xor_sync(0xffffffffu, w, 2);
+                w |= __shfl_xor_sync(0xffffffffu, w, 4);
+                const uint32_t byte = (j0 + u) * 16 + (lane >> 3) * 4;
+                if ((lane & 7) == 0 && byte < row_bytes) *reinterpret_cast<uint32_t *>(o + byte) = w;
+            }
+        }
+    }
+}
+
 qz_status bin_encode_rows(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, uint32_t row_bytes,
                           uint8_t *d_out) {
     if (count == 0 || row_bytes == 0) return QZ_OK;
+    const bool v4 = dim % 4 == 0 && row_bytes % 4 == 0 && ((uintptr_t)d_data & 15) == 0 && ((uintptr_t)d_out & 3) == 0;
+    if (v4) {
+        uint64_t blocks = (count + 7) / 8;
+        const uint64_t cap = (uint64_t)ctx->sm_count * 8;
+        if (blocks > cap) blocks = cap;
+        bin_encode_v4_kernel<<<(uint32_t)blocks, 256, 0, ctx->stream>>>(d_data, count, dim, row_bytes, d_out);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "bin_encode_v4_kernel");
+        ctx->launches++;
+        return QZ_OK;
+    }
     const uint64_t total = count * ((row_bytes + 3) / 4);
     uint64_t blocks = (total + 7) / 8;
     const uint64_t cap = (uint64_t)ctx->sm_count * 32;
@@ -93,6 +139,16 @@ __device__ __forceinline__ uint32_t u8_code_of(float v, float alpha, float offse
     return (uint32_t)__float2int_rz(t);
 }
 
+// Same code, without the IEEE division on the common path: q' = (v - offset) * (1 / alpha) is within 2^-22 relative
+// of the true quotient, so for q' in [-1, 128] it is off by < 4e-5; whenever q' is at least 1e-3 away from every
+// integer, trunc(clamp(q')) == trunc(clamp(fl((v - offset) / alpha))).  Everything else — near an integer, NaN,
+// infinities, |q'| >= 2^23 (rint(q') == q'), alpha == 0 — takes the exact division above.
+__device__ __forceinline__ uint32_t u8_code_fast(float v, float alpha, float inv_alpha, float offset) {
+    const float q = __fmul_rn(__fsub_rn(v, offset), inv_alpha);
+    if (!(fabsf(__fsub_rn(q, rintf(q))) >= 1e-3f)) return u8_code_of(v, alpha, offset);
+    return (uint32_t)__float2int_rz(fminf(fmaxf(q, 0.0f), 127.0f));
+}
+
 struct U8EncodeParams {
     const float *data;  // [count][dim]
     uint64_t count;
@@ -108,6 +164,9 @@ __global__ void __launch_bounds__(256) u8_encode_kernel(U8EncodeParams p) {
     const uint32_t words = p.actual_dim / 4;
     const uint32_t pad = u8_code_of(p.distance == kDot ? 0.0f : p.offset, p.alpha, p.offset);  // u8.rs:84-93
     const bool vec4 = (p.dim % 4 == 0) && (((uintptr_t)p.data & 15) == 0);
+    // a subnormal reciprocal has lost precision: NaN sends every element down the exact path
+    const float rcp = __fdiv_rn(1.0f, p.alpha);
+    const float inv_alpha = (fabsf(rcp) >= FLT_MIN && fabsf(rcp) <= FLT_MAX) ? rcp : __uint_as_float(0x7fc00000u);
     for (uint64_t row = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < p.count; row += nwarps) {
         const float *v = p.data + row * p.dim;
         uint32_t *o = reinterpret_cast<uint32_t *>(p.out + row * (uint64_t)(p.actual_dim + 4));
@@ -116,11 +175,11 @@ __global__ void __launch_bounds__(256) u8_encode_kernel(U8EncodeParams p) {
             const uint32_t i = 4 * w;
             uint32_t c0, c1, c2, c3;
             if (vec4 && i + 3 < p.dim) {
-                const float4 f = *reinterpret_cast<const float4 *>(v + i);
-                c0 = u8_code_of(f.x, p.alpha, p.offset);
-                c1 = u8_code_of(f.y, p.alpha, p.offset);
-                c2 = u8_code_of(f.z, p.alpha, p.offset);
-                c3 = u8_code_of(f.w, p.alpha, p.offset);
+                const float4 f = __ldcs(reinterpret_cast<const float4 *>(v + i));
+                c0 = u8_code_fast(f.x, p.alpha, inv_alpha, p.offset);
+                c1 = u8_code_fast(f.y, p.alpha, inv_alpha, p.offset);
+                c2 = u8_code_fast(f.z, p.alpha, inv_alpha, p.offset);
+                c3 = u8_code_fast(f.w, p.alpha, inv_alpha, p.offset);
             } else {
                 c0 = i < p.dim ? u8_code_of(v[i], p.alpha, p.offset) : pad;
                 c1 = i + 1 < p.dim ? u8_code_of(v[i + 1], p.alpha, p.offset) : pad;
@@ -174,20 +233,44 @@ struct SelectPass {
     uint32_t hi_shift;         // prefix compare: key >> hi_shift == prefix[r]  (hi_shift = 32 => no prefix)
     uint32_t prefix[2];
     uint32_t *hist;  // [2][2048]
+    const uint64_t *ids;  // optional: rows of the sample inside `data`
+    uint32_t dim;
 };
 
+// One element into the CTA histograms.  Lanes of a warp that hit the same digit are combined first (match.any) and
+// one lane adds their count: on real data most keys share a few sign/exponent digits in the first pass, and
+// same-address shared-memory atomics serialise.
+__device__ __forceinline__ void select_hist_add(uint32_t (*h)[2048], const SelectPass &p, float x, uint32_t mask) {
+    const uint32_t key = f32_order_bits(__float_as_uint(x));
+    const uint32_t hi = p.hi_shift >= 32 ? 0u : key >> p.hi_shift;
+    const uint32_t d = (key >> p.shift) & mask;
+    const unsigned act = __activemask();
+    const unsigned peers = __match_any_sync(act, d);
+    const unsigned b0 = __ballot_sync(act, hi == p.prefix[0]), b1 = __ballot_sync(act, hi == p.prefix[1]);
+    if ((threadIdx.x & 31) == (uint32_t)(__ffs(peers) - 1)) {
+        const uint32_t c0 = __popc(peers & b0), c1 = __popc(peers & b1);
+        if (c0) atomicAdd(&h[0][d], c0);
+        if (c1) atomicAdd(&h[1][d], c1);
+    }
+}
+
+// ids == nullptr: the n values at data[0 .. n).  Otherwise the sample is read in place, n / dim rows data[ids[r] * dim ..]
+// (one CTA per row at a time) — no gathered copy of the sample is materialised.
 __global__ void __launch_bounds__(256) select_hist_kernel(SelectPass p) {
     __shared__ uint32_t h[2][2048];
     for (uint32_t i = threadIdx.x; i < 4096; i += blockDim.x) (&h[0][0])[i] = 0;
     __syncthreads();
     const uint32_t mask = (1u << p.bits) - 1;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < p.n; i += stride) {
-        const uint32_t key = f32_order_bits(__float_as_uint(p.data[i]));
-        const uint32_t hi = p.hi_shift >= 32 ? 0u : key >> p.hi_shift;
-        const uint32_t d = (key >> p.shift) & mask;
-        if (hi == p.prefix[0]) atomicAdd(&h[0][d], 1u);
-        if (hi == p.prefix[1]) atomicAdd(&h[1][d], 1u);
+    if (p.ids == nullptr) {
+        const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+        for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < p.n; i += stride)
+            select_hist_add(h, p, p.data[i], mask);
+    } else {
+        const uint64_t n_rows = p.n / p.dim;
+        for (uint64_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
+            const float *src = p.data + p.ids[r] * p.dim;
+            for (uint32_t j = threadIdx.x; j < p.dim; j += blockDim.x) select_hist_add(h, p, src[j], mask);
+        }
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < 4096; i += blockDim.x) {
@@ -243,7 +326,8 @@ qz_status read_minmax(qz_ctx *ctx, const uint32_t *d_mm, float *mn, float *mx) {
 }
 
 // the values at ascending ranks r0 and r1 of a device array (exact, 3 histogram passes)
-qz_status dev_select2(qz_ctx *ctx, const float *d_vals, uint64_t n, uint64_t r0, uint64_t r1, float *v0, float *v1) {
+qz_status dev_select2(qz_ctx *ctx, const float *d_vals, uint64_t n, uint64_t r0, uint64_t r1, float *v0, float *v1,
+                      const uint64_t *d_ids, uint32_t dim) {
     uint32_t *d_hist = nullptr;
     QZ_CUDA(ctx, cudaMalloc((void **)&d_hist, 4096 * sizeof(uint32_t)));
     std::vector<uint32_t> h(4096);
@@ -254,7 +338,7 @@ qz_status dev_select2(qz_ctx *ctx, const float *d_vals, uint64_t n, uint64_t r0,
     for (int pass = 0; pass < 3 && st == QZ_OK; pass++) {
         cudaError_t e = cudaMemsetAsync(d_hist, 0, 4096 * sizeof(uint32_t), ctx->stream);
         if (e != cudaSuccess) { st = cuda_fail(ctx, e, "select memset"); break; }
-        SelectPass p{d_vals, n, shifts[pass], bits[pass], pass == 0 ? 32u : shifts[pass - 1], {prefix[0], prefix[1]}, d_hist};
+        SelectPass p{d_vals, n, shifts[pass], bits[pass], pass == 0 ? 32u : shifts[pass - 1], {prefix[0], prefix[1]}, d_hist, d_ids, dim};
         select_hist_kernel<<<grid_for(ctx, n, 256 * 32, 4), 256, 0, ctx->stream>>>(p);
         st = launched(ctx, "select_hist_kernel");
         if (st != QZ_OK) break;

@@ -14,7 +14,8 @@ qz_status bin_encode_rows(qz_ctx *ctx, const float *d_data, uint64_t count, uint
                           uint8_t *d_out);
 qz_status dev_minmax(qz_ctx *ctx, const float *d_data, uint64_t n, uint32_t *d_mm, bool init);
 qz_status read_minmax(qz_ctx *ctx, const uint32_t *d_mm, float *mn, float *mx);
-qz_status dev_select2(qz_ctx *ctx, const float *d_vals, uint64_t n, uint64_t r0, uint64_t r1, float *v0, float *v1);
+qz_status dev_select2(qz_ctx *ctx, const float *d_vals, uint64_t n, uint64_t r0, uint64_t r1, float *v0, float *v1,
+                      const uint64_t *d_ids, uint32_t dim);
 qz_status launch_u8_encode(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, int distance, int invert,
                            float alpha, float offset, uint8_t *d_out);
 qz_status launch_gather_rows(qz_ctx *ctx, const float *d_data, uint32_t dim, const uint64_t *d_ids, uint64_t n_ids,
@@ -70,8 +71,9 @@ static void u8_params(float mn, float mx, int distance, int invert, float *alpha
 }
 
 // quantile.rs:53-70 on `len` sampled values resident on the device
+// (d_ids != nullptr: the sample is rows d_ids[0 .. len / dim) of d_vals, read in place)
 static qz_status quantile_interval(qz_ctx *ctx, const float *d_vals, uint64_t len, uint64_t slice_size, float q,
-                                   bool *found, float *lo, float *hi) {
+                                   bool *found, float *lo, float *hi, const uint64_t *d_ids = nullptr, uint32_t dim = 0) {
     *found = false;
     if (len < 4) return QZ_OK;
     const float fb = (float)slice_size * (1.0f - q) / 2.0f;  // vector count, not value count (quantile.rs:55)
@@ -79,7 +81,7 @@ static qz_status quantile_interval(qz_ctx *ctx, const float *d_vals, uint64_t le
     uint64_t cut = std::min((len - 1) / 2, b);
     cut = std::max<uint64_t>(cut, 1);
     if (len < 2 * cut + 3) return QZ_OK;  // fewer than 2 values remain (quantile.rs:63-65)
-    QZ_TRY(dev_select2(ctx, d_vals, len, cut + 1, len - cut - 1, lo, hi));
+    QZ_TRY(dev_select2(ctx, d_vals, len, cut + 1, len - cut - 1, lo, hi, d_ids, dim));
     *found = true;
     return QZ_OK;
 }
@@ -118,18 +120,14 @@ qz_status qz_u8_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uin
             for (uint64_t id : ids)
                 if (id >= count) return fail(ctx, QZ_ARGUMENTS, "qz_u8_encode: sample id out of range");
             uint64_t *d_ids = nullptr;
-            float *d_sample = nullptr;
             cudaError_t e = cudaMalloc((void **)&d_ids, ids.size() * sizeof(uint64_t));
-            if (e == cudaSuccess) e = cudaMalloc((void **)&d_sample, ids.size() * (size_t)dim * sizeof(float));
             if (e == cudaSuccess)
                 e = cudaMemcpyAsync(d_ids, ids.data(), ids.size() * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream);
             qz_status st = e == cudaSuccess ? QZ_OK : cuda_fail(ctx, e, "qz_u8_encode: sample alloc");
-            if (st == QZ_OK) st = launch_gather_rows(ctx, d_data, dim, d_ids, ids.size(), d_sample);
             if (st == QZ_OK)
-                st = quantile_interval(ctx, d_sample, ids.size() * (uint64_t)dim, ids.size(), *quantile, &found, &lo, &hi);
+                st = quantile_interval(ctx, d_data, ids.size() * (uint64_t)dim, ids.size(), *quantile, &found, &lo, &hi, d_ids, dim);
             cudaStreamSynchronize(ctx->stream);
             cudaFree(d_ids);
-            cudaFree(d_sample);
             if (st != QZ_OK) return st;
         }
         if (found) {
