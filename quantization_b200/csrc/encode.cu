@@ -245,8 +245,15 @@ __device__ __forceinline__ void select_hist_add(uint32_t (*h)[2048], const Selec
     const uint32_t hi = p.hi_shift >= 32 ? 0u : key >> p.hi_shift;
     const uint32_t d = (key >> p.shift) & mask;
     const unsigned act = __activemask();
+    const bool m0 = hi == p.prefix[0], m1 = hi == p.prefix[1];
+    const unsigned b0 = __ballot_sync(act, m0), b1 = __ballot_sync(act, m1);
+    if ((b0 | b1) == 0) return;  // passes 2 and 3: almost no key carries a selected prefix
+    if (__popc(b0 | b1) <= 4) {  // (warp-uniform branches: match.any below is executed by all of `act` or none)
+        if (m0) atomicAdd(&h[0][d], 1u);
+        if (m1) atomicAdd(&h[1][d], 1u);
+        return;
+    }
     const unsigned peers = __match_any_sync(act, d);
-    const unsigned b0 = __ballot_sync(act, hi == p.prefix[0]), b1 = __ballot_sync(act, hi == p.prefix[1]);
     if ((threadIdx.x & 31) == (uint32_t)(__ffs(peers) - 1)) {
         const uint32_t c0 = __popc(peers & b0), c1 = __popc(peers & b1);
         if (c0) atomicAdd(&h[0][d], c0);
