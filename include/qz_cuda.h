@@ -113,6 +113,25 @@ QZ_API qz_status qz_u8_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t cou
                                   uint64_t n_sample, uint64_t seed, const volatile int32_t *stop, uint8_t *d_out,
                                   float *alpha, float *offset, float *multiplier);
 
+/* Sharded encode: the rows of one corpus live on several GPUs, one process each.  encode's global
+ * quantities are split out so the caller can combine them across ranks (an all-reduce of two floats; an
+ * all-gather of the sampled rows when a quantile is asked for) and every rank then encodes its own rows with the
+ * same (min, max) — the resulting shards are byte-identical to slices of a single-GPU qz_u8_encode.
+ *   qz_u8_minmax_dev        find_min_max_from_iter (quantile.rs:5-19) over this rank's rows; count == 0 returns
+ *                           (f32::MAX, f32::MIN), the fold's identity
+ *   qz_u8_quantile_dev      find_quantile_interval's two order statistics (quantile.rs:53-70) over `n_rows` sampled
+ *                           rows resident on the device; `slice_size` = the number of sampled vectors of the WHOLE
+ *                           corpus (min(count, 100000), quantile.rs:30); *found = 0 keeps (min, max)
+ *   qz_u8_encode_range_dev  the second half of encode (u8.rs:73-128) with (min, max) given */
+QZ_API qz_status qz_u8_minmax_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, float *min_out,
+                                  float *max_out);
+QZ_API qz_status qz_u8_quantile_dev(qz_ctx *ctx, const float *d_sample, uint64_t n_rows, uint32_t dim,
+                                    uint64_t slice_size, float quantile, int32_t *found, float *lo, float *hi);
+QZ_API qz_status qz_u8_encode_range_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim,
+                                        int32_t distance, int32_t invert, float min_value, float max_value,
+                                        const volatile int32_t *stop, uint8_t *d_out, float *alpha, float *offset,
+                                        float *multiplier);
+
 /* Batched multi-query search (BASELINE config 5): nq f32 queries [nq][dim] against every row, the k best
  * per query.  One call = encode_query for each query (u8.rs:290-329), the nq x count x actual_dim integer
  * contraction on the tensor cores (tcgen05 kind::i8, the same sums impl_score_dot_* returns per pair,

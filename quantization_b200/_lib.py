@@ -35,6 +35,10 @@ _SIGS = {
                                  C.c_uint64, vp, vp, f32p, f32p, f32p]),
     "qz_u8_encode_dev": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, f32p, vp, C.c_uint64,
                                      C.c_uint64, vp, vp, f32p, f32p, f32p]),
+    "qz_u8_minmax_dev": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, f32p, f32p]),
+    "qz_u8_quantile_dev": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_uint64, C.c_float, C.POINTER(C.c_int32), f32p, f32p]),
+    "qz_u8_encode_range_dev": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, C.c_float, C.c_float, vp, vp,
+                                           f32p, f32p, f32p]),
     "qz_u8_search_batch": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp]),
     "qz_u8_search_batch_dev": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp]),
     "qz_search_topk": (C.c_int32, [vp, vp, C.c_uint32, C.c_int32, vp, vp, u32p]),

@@ -172,6 +172,56 @@ qz_status qz_u8_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uin
     return QZ_OK;
 }
 
+qz_status qz_u8_minmax_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, float *min_out,
+                           float *max_out) {
+    if (!ctx || !min_out || !max_out) return fail(ctx, QZ_ARGUMENTS, "qz_u8_minmax_dev: NULL argument");
+    if (count && (!d_data || dim == 0)) return fail(ctx, QZ_ARGUMENTS, "qz_u8_minmax_dev: NULL data");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    QZ_CUDA(ctx, cudaSetDevice(ctx->device));
+    QZ_TRY(ensure_io(ctx, 256));
+    uint32_t *d_mm = reinterpret_cast<uint32_t *>(ctx->d_io);
+    QZ_TRY(dev_minmax(ctx, d_data, count * (uint64_t)dim, d_mm, true));
+    return read_minmax(ctx, d_mm, min_out, max_out);
+}
+
+qz_status qz_u8_quantile_dev(qz_ctx *ctx, const float *d_sample, uint64_t n_rows, uint32_t dim, uint64_t slice_size,
+                             float quantile, int32_t *found, float *lo, float *hi) {
+    if (!ctx || !found || !lo || !hi) return fail(ctx, QZ_ARGUMENTS, "qz_u8_quantile_dev: NULL argument");
+    *found = 0;
+    *lo = *hi = 0.0f;
+    if (n_rows == 0 || dim == 0) return QZ_OK;
+    if (!d_sample) return fail(ctx, QZ_ARGUMENTS, "qz_u8_quantile_dev: NULL sample");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    QZ_CUDA(ctx, cudaSetDevice(ctx->device));
+    bool f = false;
+    QZ_TRY(quantile_interval(ctx, d_sample, n_rows * (uint64_t)dim, slice_size, quantile, &f, lo, hi));
+    *found = f ? 1 : 0;
+    return QZ_OK;
+}
+
+qz_status qz_u8_encode_range_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, int32_t distance,
+                                 int32_t invert, float min_value, float max_value, const volatile int32_t *stop,
+                                 uint8_t *d_out, float *alpha, float *offset, float *multiplier) {
+    if (!ctx || !alpha || !offset || !multiplier) return fail(ctx, QZ_ARGUMENTS, "qz_u8_encode_range_dev: NULL argument");
+    if (distance < QZ_DOT || distance > QZ_L2 || dim == 0) return fail(ctx, QZ_ARGUMENTS, "qz_u8_encode_range_dev: bad parameters");
+    if (count && (!d_data || !d_out)) return fail(ctx, QZ_ARGUMENTS, "qz_u8_encode_range_dev: NULL data");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    QZ_CUDA(ctx, cudaSetDevice(ctx->device));
+    u8_params(min_value, max_value, distance, invert, alpha, offset, multiplier);
+    const uint32_t row_bytes = qz_u8_row_bytes(dim);
+    const uint64_t chunk = std::max<uint64_t>(1, kChunkBytes / ((uint64_t)dim * 4));
+    for (uint64_t r = 0; r < count; r += chunk) {
+        if (stopped(stop)) {
+            cudaStreamSynchronize(ctx->stream);
+            return QZ_STOPPED;
+        }
+        const uint64_t n = std::min(chunk, count - r);
+        QZ_TRY(launch_u8_encode(ctx, d_data + r * dim, n, dim, distance, invert, *alpha, *offset, d_out + r * row_bytes));
+    }
+    QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return QZ_OK;
+}
+
 qz_status qz_u8_encode(qz_ctx *ctx, const float *data, uint64_t count, uint32_t dim, int32_t distance, int32_t invert,
                        const float *quantile, const uint64_t *sample_ids, uint64_t n_sample, uint64_t seed,
                        const volatile int32_t *stop, uint8_t *out_storage, float *alpha, float *offset,

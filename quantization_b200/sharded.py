@@ -150,3 +150,114 @@ class ShardedSearch:
         s, i = s.cpu().numpy(), i.cpu().numpy().view(np.uint32)
         n = k if total_count is None else min(k, total_count)
         return s[:n].copy(), i[:n].copy()
+
+
+# =====================================================================================================
+# sharded encode ("Encode: shard rows the same way; min/max needs one all-reduce of 2 floats")
+# =====================================================================================================
+QUANTILE_SAMPLE = 100_000  # quantile.rs:30
+
+
+def sample_ids(count, n, seed=0):
+    """The library's default quantile sample (csrc/encode_api.cu pick_sample_ids): n distinct ascending ids from the
+    affine walk x -> x + a (mod count).  The reference draws a randomly keyed permutation (quantile.rs:32-34)."""
+    import math
+    if n >= count:
+        return np.arange(count, dtype=np.uint64)
+    a = int(float(count) * 0.6180339887498949) | 1
+    while math.gcd(a, count) != 1:
+        a += 2
+    a %= count
+    if count < (1 << 40):  # a * j < 2^57: exact in u64
+        return np.sort((np.arange(n, dtype=np.uint64) * np.uint64(a) + np.uint64(seed % count)) % np.uint64(count))
+    return np.sort(np.array([(a * j + seed % count) % count for j in range(n)], dtype=np.uint64))
+
+
+class ShardedEncodeU8:
+    """EncodedVectorsU8::encode (u8.rs:34-140) for a corpus whose rows are spread over the ranks (rank g holds the
+    f32 rows shard_range(count, g, G)).  Global quantities are combined across ranks, then every rank encodes its own
+    rows; the shards are byte-identical to slices of a single-GPU encode and (alpha, offset, multiplier) are the same
+    on every rank.  Exchanges: one all-reduce(MIN) + all-reduce(MAX) of a float each; with a quantile, one
+    all-gather of the sampled rows (<= 100 000 x dim f32 in total) so that every rank selects the same two order
+    statistics.  The device steps are injectable like ShardedSearch's, for the gloo tests."""
+
+    def __init__(self, ctx=None, group=None, device=None, *, local_minmax=None, local_quantile=None, local_encode=None,
+                 gather_rows=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.ctx, self.group = torch, dist, ctx, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.device = device if device is not None else torch.device("cpu")
+        self._minmax = local_minmax or self._gpu_minmax
+        self._quantile = local_quantile or self._gpu_quantile
+        self._encode = local_encode or self._gpu_encode
+        self._gather_rows = gather_rows or (lambda d_rows, ids: d_rows[self.torch.as_tensor(ids.astype(np.int64), device=d_rows.device)])
+
+    # ---- device steps (libqz_cuda) -------------------------------------------------------------------
+    def _gpu_minmax(self, d_rows):
+        mn, mx = C.c_float(), C.c_float()
+        n, dim = d_rows.shape
+        self.ctx.check(self.ctx._L.qz_u8_minmax_dev(self.ctx.handle, C.c_void_p(d_rows.data_ptr()), n, dim,
+                                                    C.byref(mn), C.byref(mx)))
+        return mn.value, mx.value
+
+    def _gpu_quantile(self, d_sample, slice_size, quantile):
+        found, lo, hi = C.c_int32(), C.c_float(), C.c_float()
+        n, dim = d_sample.shape
+        self.ctx.check(self.ctx._L.qz_u8_quantile_dev(self.ctx.handle, C.c_void_p(d_sample.data_ptr()), n, dim, slice_size,
+                                                      quantile, C.byref(found), C.byref(lo), C.byref(hi)))
+        return (lo.value, hi.value) if found.value else None
+
+    def _gpu_encode(self, d_rows, vp_local, mn, mx, id_base):
+        from .encoded_vectors_u8 import EncodedVectorsU8
+        ix = EncodedVectorsU8(self.ctx, None, vp_local, 0.0, 0.0, 0.0, id_base)
+        a, o, m = C.c_float(), C.c_float(), C.c_float()
+        n, dim = d_rows.shape
+        self.ctx.check(self.ctx._L.qz_u8_encode_range_dev(self.ctx.handle, C.c_void_p(d_rows.data_ptr()), n, dim,
+                                                          int(vp_local.distance_type), int(vp_local.invert), mn, mx, None,
+                                                          C.c_void_p(ix.storage_dev), C.byref(a), C.byref(o), C.byref(m)))
+        self.ctx.check(self.ctx._L.qz_u8_index_set_params(ix.handle, a.value, o.value, m.value))
+        ix.alpha, ix.offset, ix.multiplier = np.float32(a.value), np.float32(o.value), np.float32(m.value)
+        return ix
+
+    # ---- the encode ------------------------------------------------------------------------------------
+    def encode(self, d_rows, vector_parameters, quantile=None, ids=None, seed=0):
+        """d_rows: this rank's [hi - lo, dim] f32 rows (a torch tensor on self.device; the caller has synchronised
+        its producer); vector_parameters describes the WHOLE corpus.  Returns the rank's shard (id_base = lo)."""
+        from .encoded_vectors import VectorParameters
+        t, dist = self.torch, self.dist
+        vp = vector_parameters
+        lo, hi = shard_range(vp.count, self.rank, self.world)
+        assert tuple(d_rows.shape) == (hi - lo, vp.dim), "rank holds rows shard_range(count, rank, world)"
+        mn, mx = self._minmax(d_rows)
+        if self.world > 1:  # min / max are exact under any grouping: the sharded fold equals quantile.rs:5-19
+            d_mn = t.tensor([mn], dtype=t.float32, device=self.device)
+            d_mx = t.tensor([mx], dtype=t.float32, device=self.device)
+            dist.all_reduce(d_mn, op=dist.ReduceOp.MIN, group=self.group)
+            dist.all_reduce(d_mx, op=dist.ReduceOp.MAX, group=self.group)
+            mn, mx = float(d_mn.item()), float(d_mx.item())
+        if quantile is not None and vp.count >= 127 and quantile < 1.0:  # quantile.rs:27-29
+            slice_size = min(vp.count, QUANTILE_SAMPLE)
+            ids = sample_ids(vp.count, slice_size, seed) if ids is None else np.sort(np.asarray(ids, np.uint64))
+            mine = ids[(ids >= lo) & (ids < hi)] - np.uint64(lo)
+            d_mine = self._gather_rows(d_rows, mine)
+            if self.world > 1:
+                # equal-size all-gather: pad every rank's sample to the largest share, then drop the padding;
+                # ranks own ascending id ranges, so concatenation in rank order keeps the sample in id order
+                counts = [int(((ids >= a) & (ids < b)).sum()) for a, b in (shard_range(vp.count, r, self.world) for r in range(self.world))]
+                cap = max(counts)
+                d_pad = t.zeros((cap, vp.dim), dtype=t.float32, device=self.device)
+                d_pad[:counts[self.rank]] = d_mine
+                d_all = t.zeros((self.world * cap, vp.dim), dtype=t.float32, device=self.device)
+                dist.all_gather_into_tensor(d_all, d_pad, group=self.group)
+                d_sample = t.cat([d_all[r * cap: r * cap + counts[r]] for r in range(self.world)]).contiguous()
+            else:
+                d_sample = d_mine.contiguous()
+            if self.device.type == "cuda":
+                t.cuda.synchronize(self.device)  # the context runs on its own stream
+            iv = self._quantile(d_sample, slice_size, float(quantile))
+            if iv is not None:
+                mn, mx = iv
+        vp_local = VectorParameters(vp.dim, hi - lo, vp.distance_type, vp.invert)
+        return self._encode(d_rows, vp_local, mn, mx, lo)

@@ -73,3 +73,41 @@ def test_sharded_search_class_world1():
     assert np.array_equal(i, wi) and np.array_equal(s.view(np.uint32), ws.view(np.uint32))
     torch.cuda.set_stream(torch.cuda.default_stream(0))
     ix.close()
+
+
+@pytest.mark.parametrize("G", [2, 3])
+@pytest.mark.parametrize("count,dim,quantile,dist", [(20_000, 1536, None, qz.DistanceType.Dot), (150_000, 64, 0.99, qz.DistanceType.L2),
+                                                     (3000, 33, 0.9, qz.DistanceType.L1)])
+def test_sharded_encode_steps_on_one_device(ctx, G, count, dim, quantile, dist):
+    """the three C-ABI steps of a sharded encode (qz_u8_minmax_dev / qz_u8_quantile_dev / qz_u8_encode_range_dev), run
+    for G row shards of one device-resident matrix with the reductions done on the host: every shard is a byte
+    slice of the single-GPU qz_u8_encode_dev result and the Metadata scalars agree"""
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev); g.manual_seed(3)
+    data = torch.rand((count, dim), generator=g, device=dev) * 4 - 1
+    torch.cuda.synchronize()
+    vp = qz.VectorParameters(dim, count, dist, True)
+    whole = qz.EncodedVectorsU8.encode_dev(data.data_ptr(), vp, quantile, ctx=ctx, seed=1)
+    ref = whole.download()
+    enc = S.ShardedEncodeU8(ctx, device=dev)
+    parts = [data[lo:hi] for lo, hi in (S.shard_range(count, r, G) for r in range(G))]
+    mm = [enc._gpu_minmax(p) for p in parts]
+    mn, mx = min(m[0] for m in mm), max(m[1] for m in mm)
+    if quantile is not None:
+        slice_size = min(count, S.QUANTILE_SAMPLE)
+        ids = S.sample_ids(count, slice_size, 1)
+        sample = data[torch.as_tensor(ids.astype(np.int64), device=dev)].contiguous()
+        torch.cuda.synchronize()
+        iv = enc._gpu_quantile(sample, slice_size, quantile)
+        assert iv is not None
+        mn, mx = iv
+    rb = qz.EncodedVectorsU8.get_quantized_vector_size(vp)
+    for r, p in enumerate(parts):
+        lo, hi = S.shard_range(count, r, G)
+        ix = enc._gpu_encode(p, qz.VectorParameters(dim, hi - lo, dist, True), mn, mx, lo)
+        assert (ix.alpha, ix.offset, ix.multiplier) == (whole.alpha, whole.offset, whole.multiplier)
+        assert np.array_equal(ix.download(), ref[lo * rb: hi * rb]), f"shard {r} of {G} is not a slice of the global encode"
+        # and it scans with global ids
+        q = whole.encode_query(O.uniform(9, dim))
+        s, i = ix.search_top_k(q, 10, True)
+        assert i.min() >= lo and i.max() < hi

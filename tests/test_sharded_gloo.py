@@ -94,3 +94,48 @@ def test_key_roundtrip_and_order():
         assert all(int(k[j]) == O.make_key(float(s[j]), int(i[j]), lg) for j in range(len(s)))
     k = S.results_to_keys(s, i, True)
     assert k[6] > k[0]  # equal scores: the lower id has the larger key
+
+
+# ---- sharded encode: min/max all-reduce, sample all-gather, byte-identical shards ------------------
+def _encode_worker(rank, world, port, count, dim, quantile, out):
+    import ctypes as C
+    from oracle import oracle as OM
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        data = O.uniform(42, count * dim, -1.0, 3.0).reshape(count, dim)
+        ids = np.sort(np.random.default_rng(5).permutation(count)[: min(count, 300)]).astype(np.uint64) if quantile else None
+        full = O.OracleU8.encode(data, O.L2, True, quantile, ids)
+        lo, hi = S.shard_range(count, rank, world)
+        got = {}
+
+        def local_encode(rows, vp_local, mn, mx, id_base):  # stand-in for qz_u8_encode_range_dev
+            a, o = C.c_float(), C.c_float()
+            OM._lib.qzo_u8_alpha_offset(C.c_float(mn), C.c_float(mx), C.byref(a), C.byref(o))
+            r = np.ascontiguousarray(rows.numpy())
+            st = np.empty(r.shape[0] * (O.u8_actual_dim(dim) + 4), np.uint8)
+            OM._lib.qzo_u8_encode(OM._p(r, OM._f32p), C.c_uint64(r.shape[0]), C.c_uint32(dim), C.c_int(O.L2), C.c_int(1), a, o,
+                                  OM._p(st, OM._u8p))
+            got.update(alpha=a.value, offset=o.value, id_base=id_base)
+            return st
+
+        enc = S.ShardedEncodeU8(
+            None, local_minmax=lambda rows: O.minmax(rows.numpy()),
+            local_quantile=lambda sample, slice_size, q: O.quantile_interval(sample.numpy(), count, slice_size, q),
+            local_encode=local_encode)
+        from quantization_b200 import VectorParameters, DistanceType
+        st = enc.encode(torch.from_numpy(data[lo:hi].copy()), VectorParameters(dim, count, DistanceType.L2, True), quantile, ids)
+        rb = full.stride
+        ok = (np.array_equal(st, full.storage[lo * rb: hi * rb]) and np.float32(got["alpha"]) == full.alpha
+              and np.float32(got["offset"]) == full.offset and got["id_base"] == lo)
+        out[rank] = int(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("count,dim,quantile", [(1000, 33, None), (1000, 33, 0.9), (131, 16, 0.99), (5, 8, None)])
+def test_sharded_encode_is_a_slice_of_the_global_encode(world, count, dim, quantile):
+    out = mp.Manager().list([0] * world)
+    mp.spawn(_encode_worker, args=(world, _free_port(), count, dim, quantile, out), nprocs=world, join=True)
+    assert list(out) == [1] * world
