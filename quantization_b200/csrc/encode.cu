@@ -171,7 +171,28 @@ __global__ void __launch_bounds__(256) u8_encode_kernel(U8EncodeParams p) {
         const float *v = p.data + row * p.dim;
         uint32_t *o = reinterpret_cast<uint32_t *>(p.out + row * (uint64_t)(p.actual_dim + 4));
         uint32_t s1 = 0, s2 = 0;
-        for (uint32_t w = lane; w < words; w += 32) {
+        uint32_t w_first = lane;
+        if (vec4) {
+            // whole float4 words, four per lane in flight before the first use (the pad words, if any, and odd
+            // shapes go through the loop below)
+            const uint32_t full = p.dim / 4;  // words made of source floats only
+            for (; w_first + 96 < full; w_first += 128) {
+                float4 f[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) f[u] = __ldcs(reinterpret_cast<const float4 *>(v + 4 * (w_first + 32 * u)));
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t c0 = u8_code_fast(f[u].x, p.alpha, inv_alpha, p.offset);
+                    const uint32_t c1 = u8_code_fast(f[u].y, p.alpha, inv_alpha, p.offset);
+                    const uint32_t c2 = u8_code_fast(f[u].z, p.alpha, inv_alpha, p.offset);
+                    const uint32_t c3 = u8_code_fast(f[u].w, p.alpha, inv_alpha, p.offset);
+                    o[1 + w_first + 32 * u] = c0 | (c1 << 8) | (c2 << 16) | (c3 << 24);
+                    s1 += c0 + c1 + c2 + c3;
+                    s2 += c0 * c0 + c1 * c1 + c2 * c2 + c3 * c3;
+                }
+            }
+        }
+        for (uint32_t w = w_first; w < words; w += 32) {
             const uint32_t i = 4 * w;
             uint32_t c0, c1, c2, c3;
             if (vec4 && i + 3 < p.dim) {

@@ -35,8 +35,17 @@ static uint64_t gcd64(uint64_t a, uint64_t b) {
     return a;
 }
 
-// `n` distinct ids in [0,count): the caller's list, or (the reference draws a random permutation,
-// quantile.rs:32-34 / pq.rs:300-302) an affine permutation i -> (a*i + b) mod count keyed by seed.
+static inline uint64_t splitmix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// `n` distinct ids in [0,count), ascending: the caller's list, or (the reference draws them from a randomly keyed
+// permutation, quantile.rs:32-34 / pq.rs:300-302 — permutation_iterator is a Feistel network too) the first n
+// outputs of a 4-round Feistel permutation of [0, 2^bits) keyed by `seed`, cycle-walked into [0, count).
+// quantization_b200/sharded.py::sample_ids is the same function (sharded encode needs the ids on every rank).
 std::vector<uint64_t> pick_sample_ids(uint64_t count, uint64_t n, const uint64_t *ids, uint64_t n_ids, uint64_t seed) {
     std::vector<uint64_t> out;
     if (ids) {
@@ -44,33 +53,40 @@ std::vector<uint64_t> pick_sample_ids(uint64_t count, uint64_t n, const uint64_t
     } else if (n >= count) {
         out.resize(count);
         std::iota(out.begin(), out.end(), 0ull);
+        return out;
     } else {
-        uint64_t a = (uint64_t)((double)count * 0.6180339887498949) | 1ull;
-        while (gcd64(a, count) != 1) a += 2;
-        const uint64_t b = seed % count;
+        uint32_t bits = 2;
+        while (bits < 64 && (1ull << bits) < count) bits += 2;  // even, so the halves are equal
+        const uint32_t half = bits / 2;
+        const uint64_t mask = (1ull << half) - 1;
+        uint64_t keys[4];
+        for (int r = 0; r < 4; r++) keys[r] = splitmix64(seed * 4 + r);
+        auto perm = [&](uint64_t x) {
+            do {
+                uint64_t l = x >> half, r = x & mask;
+                for (int k = 0; k < 4; k++) {
+                    const uint64_t f = splitmix64(r ^ keys[k]) & mask;
+                    const uint64_t t = l ^ f;
+                    l = r;
+                    r = t;
+                }
+                x = (l << half) | r;
+            } while (x >= count);
+            return x;
+        };
         out.resize(n);
-        a %= count;
-        if (count <= 256 * n) {
-            // the walk x -> x + a (mod count) marks a bitmap; reading the bitmap back yields the ids already
-            // ascending (100k of 1M ids: ~0.2 ms instead of 8 ms of 128-bit modulo + std::sort)
-            std::vector<uint64_t> bits((count + 63) / 64, 0ull);
-            uint64_t x = b;
+        if (count <= 256 * n) {  // mark a bitmap and read it back: the ids come out ascending without a sort
+            std::vector<uint64_t> bm((count + 63) / 64, 0ull);
             for (uint64_t i = 0; i < n; i++) {
-                bits[x >> 6] |= 1ull << (x & 63);
-                x += a;
-                if (x >= count) x -= count;
+                const uint64_t x = perm(i);
+                bm[x >> 6] |= 1ull << (x & 63);
             }
             size_t k = 0;
-            for (size_t w = 0; w < bits.size(); w++)
-                for (uint64_t m = bits[w]; m; m &= m - 1) out[k++] = (uint64_t)w * 64 + (uint64_t)__builtin_ctzll(m);
+            for (size_t w = 0; w < bm.size(); w++)
+                for (uint64_t m = bm[w]; m; m &= m - 1) out[k++] = (uint64_t)w * 64 + (uint64_t)__builtin_ctzll(m);
             return out;
         }
-        uint64_t x = b;
-        for (uint64_t i = 0; i < n; i++) {
-            out[i] = x;
-            x += a;
-            if (x >= count) x -= count;
-        }
+        for (uint64_t i = 0; i < n; i++) out[i] = perm(i);
     }
     std::sort(out.begin(), out.end());
     return out;

@@ -158,19 +158,39 @@ class ShardedSearch:
 QUANTILE_SAMPLE = 100_000  # quantile.rs:30
 
 
+def _splitmix64(z):
+    z = z + np.uint64(0x9E3779B97F4A7C15)
+    z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return z ^ (z >> np.uint64(31))
+
+
 def sample_ids(count, n, seed=0):
-    """The library's default quantile sample (csrc/encode_api.cu pick_sample_ids): n distinct ascending ids from the
-    affine walk x -> x + a (mod count).  The reference draws a randomly keyed permutation (quantile.rs:32-34)."""
-    import math
+    """The library's default sample (csrc/encode_api.cu pick_sample_ids, same arithmetic): n distinct ascending ids —
+    the first n outputs of a 4-round Feistel permutation keyed by `seed`, cycle-walked into [0, count).  The
+    reference draws them from a randomly keyed permutation (quantile.rs:32-34)."""
     if n >= count:
         return np.arange(count, dtype=np.uint64)
-    a = int(float(count) * 0.6180339887498949) | 1
-    while math.gcd(a, count) != 1:
-        a += 2
-    a %= count
-    if count < (1 << 40):  # a * j < 2^57: exact in u64
-        return np.sort((np.arange(n, dtype=np.uint64) * np.uint64(a) + np.uint64(seed % count)) % np.uint64(count))
-    return np.sort(np.array([(a * j + seed % count) % count for j in range(n)], dtype=np.uint64))
+    bits = 2
+    while bits < 64 and (1 << bits) < count:
+        bits += 2
+    half, mask = np.uint64(bits // 2), np.uint64((1 << (bits // 2)) - 1)
+    with np.errstate(over="ignore"):
+        keys = [_splitmix64(np.uint64((seed * 4 + r) & 0xFFFFFFFFFFFFFFFF)) for r in range(4)]
+
+        def rounds(x):
+            l, r = x >> half, x & mask
+            for k in keys:
+                l, r = r, l ^ (_splitmix64(r ^ k) & mask)
+            return (l << half) | r
+
+        x = rounds(np.arange(n, dtype=np.uint64))
+        while True:
+            out = x >= np.uint64(count)
+            if not out.any():
+                break
+            x[out] = rounds(x[out])
+    return np.sort(x)
 
 
 class ShardedEncodeU8:
