@@ -144,3 +144,30 @@ def test_c4_pq_1m_x_768_codes(ctx):
     os_, oi = o.search(lut, K, True, threads=THREADS)
     assert np.allclose(np.sort(gs), np.sort(os_), rtol=1e-5, atol=0)
     assert len(set(gi.tolist()) & set(oi.tolist())) >= K - 2
+
+
+@pytest.mark.parametrize("dim", [128, 1024])
+def test_c1_u8_100k_host_path(ctx, dim):
+    """BASELINE config 1 (the reference's own bench shape, demos/benches/encode.rs:15-16, 42-49, 91-102): host f32
+    data -> encode through the host C-ABI call -> linear scan, random-access score_point and score_internal.  Inputs are
+    SURVEY 8d's (SplitMix64 seeds 42 / 43); everything is compared with the oracle on ALL 100k rows."""
+    count = 100_000
+    data = O.uniform(42, count * dim).reshape(count, dim)
+    query = O.uniform(43, dim)
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
+    g = qz.EncodedVectorsU8.encode(data, qz.VecStorageBuilder(), vp, None, lambda: False, ctx=ctx)
+    o = O.OracleU8.encode(data, 0, False)
+    assert np.array_equal(np.asarray(g.encoded_vectors), o.storage)
+    assert (g.alpha, g.offset, g.multiplier) == (o.alpha, o.offset, o.multiplier)
+    enc = g.encode_query(query)
+    assert np.array_equal(np.frombuffer(bytes(enc), np.uint8), o.encode_query(query))
+    assert np.array_equal(bits(g.score_all(enc)), bits(o.scan(o.encode_query(query))))
+    gs, gi = g.search_top_k(enc, K, True)
+    os_, oi = o.search(o.encode_query(query), K, True, threads=THREADS)
+    assert np.array_equal(gi, oi) and np.array_equal(bits(gs), bits(os_))
+    rng = np.random.default_rng(1)
+    ids = rng.integers(0, count, 5000).astype(np.uint32)  # the bench's random access pattern
+    assert np.array_equal(bits(g.score_points(enc, ids)), bits(o.scan(o.encode_query(query))[ids]))
+    ia, ib = rng.integers(0, count, 2000).astype(np.uint32), rng.integers(0, count, 2000).astype(np.uint32)
+    assert np.array_equal(bits(g.score_pairs(ia, ib)), bits(o.score_pairs(ia, ib)))
+    assert bits(np.float32(g.score_point(enc, 123)))[()] == bits(np.float32(o.score_point(o.encode_query(query), 123)))[()]
