@@ -193,6 +193,25 @@ def sample_ids(count, n, seed=0):
     return np.sort(x)
 
 
+def all_gather_sample(self, d_rows, ids, count, dim):
+    """rows `ids` (ascending, global) of a corpus whose rows are spread over the ranks -> the same [len(ids), dim]
+    matrix on every rank.  Equal-size all-gather: every rank's share is padded to the largest share and the padding
+    dropped afterwards; ranks own ascending id ranges, so concatenation in rank order keeps the sample in id order."""
+    t, dist = self.torch, self.dist
+    lo, hi = shard_range(count, self.rank, self.world)
+    mine = ids[(ids >= lo) & (ids < hi)] - np.uint64(lo)
+    d_mine = self._gather_rows(d_rows, mine)
+    if self.world == 1:
+        return d_mine.contiguous()
+    counts = [int(((ids >= a) & (ids < b)).sum()) for a, b in (shard_range(count, r, self.world) for r in range(self.world))]
+    cap = max(max(counts), 1)
+    d_pad = t.zeros((cap, dim), dtype=t.float32, device=self.device)
+    d_pad[:counts[self.rank]] = d_mine
+    d_all = t.zeros((self.world * cap, dim), dtype=t.float32, device=self.device)
+    dist.all_gather_into_tensor(d_all, d_pad, group=self.group)
+    return t.cat([d_all[r * cap: r * cap + counts[r]] for r in range(self.world)]).contiguous()
+
+
 class ShardedEncodeU8:
     """EncodedVectorsU8::encode (u8.rs:34-140) for a corpus whose rows are spread over the ranks (rank g holds the
     f32 rows shard_range(count, g, G)).  Global quantities are combined across ranks, then every rank encodes its own
@@ -260,20 +279,7 @@ class ShardedEncodeU8:
         if quantile is not None and vp.count >= 127 and quantile < 1.0:  # quantile.rs:27-29
             slice_size = min(vp.count, QUANTILE_SAMPLE)
             ids = sample_ids(vp.count, slice_size, seed) if ids is None else np.sort(np.asarray(ids, np.uint64))
-            mine = ids[(ids >= lo) & (ids < hi)] - np.uint64(lo)
-            d_mine = self._gather_rows(d_rows, mine)
-            if self.world > 1:
-                # equal-size all-gather: pad every rank's sample to the largest share, then drop the padding;
-                # ranks own ascending id ranges, so concatenation in rank order keeps the sample in id order
-                counts = [int(((ids >= a) & (ids < b)).sum()) for a, b in (shard_range(vp.count, r, self.world) for r in range(self.world))]
-                cap = max(counts)
-                d_pad = t.zeros((cap, vp.dim), dtype=t.float32, device=self.device)
-                d_pad[:counts[self.rank]] = d_mine
-                d_all = t.zeros((self.world * cap, vp.dim), dtype=t.float32, device=self.device)
-                dist.all_gather_into_tensor(d_all, d_pad, group=self.group)
-                d_sample = t.cat([d_all[r * cap: r * cap + counts[r]] for r in range(self.world)]).contiguous()
-            else:
-                d_sample = d_mine.contiguous()
+            d_sample = all_gather_sample(self, d_rows, ids, vp.count, vp.dim)
             if self.device.type == "cuda":
                 t.cuda.synchronize(self.device)  # the context runs on its own stream
             iv = self._quantile(d_sample, slice_size, float(quantile))
@@ -281,3 +287,52 @@ class ShardedEncodeU8:
                 mn, mx = iv
         vp_local = VectorParameters(vp.dim, hi - lo, vp.distance_type, vp.invert)
         return self._encode(d_rows, vp_local, mn, mx, lo)
+
+
+KMEANS_SAMPLE = 10_000  # pq.rs:286
+
+
+class ShardedEncodePQ:
+    """EncodedVectorsPQ::encode (pq.rs:56-107) for rows spread over the ranks: the <= 10 000 sampled rows of
+    find_centroids (pq.rs:278-342) are all-gathered, every rank runs the same deterministic k-means on them (768
+    chunk problems side by side, ~0.1 s — cheaper than broadcasting and waiting for one rank), then assigns its own
+    rows.  Centroids are bit-identical on every rank and to the single-GPU encode with the same sample ids, and the
+    code shards are byte slices of the single-GPU codes."""
+
+    def __init__(self, ctx=None, group=None, device=None, *, local_train=None, local_assign=None, gather_rows=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.ctx, self.group = torch, dist, ctx, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.device = device if device is not None else torch.device("cpu")
+        self._train = local_train or self._gpu_train
+        self._assign = local_assign or self._gpu_assign
+        self._gather_rows = gather_rows or (lambda d_rows, ids: d_rows[self.torch.as_tensor(ids.astype(np.int64), device=d_rows.device)])
+
+    def _gpu_train(self, d_sample, chunk_size, seed):
+        n, dim = d_sample.shape
+        cen = np.zeros((256, dim), np.float32)
+        self.ctx.check(self.ctx._L.qz_pq_train_dev(self.ctx.handle, C.c_void_p(d_sample.data_ptr()), n, dim, chunk_size, None, 0,
+                                                   seed, 100, 1e-5, None, C.c_void_p(cen.ctypes.data), None))
+        return cen
+
+    def _gpu_assign(self, d_rows, vp_local, chunk_size, centroids, id_base):
+        from .encoded_vectors_pq import EncodedVectorsPQ
+        ix = EncodedVectorsPQ(self.ctx, None, vp_local, chunk_size, centroids, id_base)
+        n, dim = d_rows.shape
+        self.ctx.check(self.ctx._L.qz_pq_assign_dev(self.ctx.handle, C.c_void_p(d_rows.data_ptr()), n, dim, chunk_size,
+                                                    C.c_void_p(ix.centroids.ctypes.data), None, C.c_void_p(ix.storage_dev)))
+        return ix
+
+    def encode(self, d_rows, vector_parameters, chunk_size, ids=None, seed=0):
+        from .encoded_vectors import VectorParameters
+        vp = vector_parameters
+        lo, hi = shard_range(vp.count, self.rank, self.world)
+        assert tuple(d_rows.shape) == (hi - lo, vp.dim), "rank holds rows shard_range(count, rank, world)"
+        ids = sample_ids(vp.count, min(vp.count, KMEANS_SAMPLE), seed) if ids is None else np.sort(np.asarray(ids, np.uint64))
+        d_sample = all_gather_sample(self, d_rows, ids, vp.count, vp.dim)
+        if self.device.type == "cuda":
+            self.torch.cuda.synchronize(self.device)  # the context runs on its own stream
+        centroids = self._train(d_sample, chunk_size, seed)
+        return self._assign(d_rows, VectorParameters(vp.dim, hi - lo, vp.distance_type, vp.invert), chunk_size, centroids, lo)

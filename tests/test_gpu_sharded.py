@@ -111,3 +111,29 @@ def test_sharded_encode_steps_on_one_device(ctx, G, count, dim, quantile, dist):
         q = whole.encode_query(O.uniform(9, dim))
         s, i = ix.search_top_k(q, 10, True)
         assert i.min() >= lo and i.max() < hi
+
+
+@pytest.mark.parametrize("G", [2, 3])
+def test_sharded_pq_encode_steps_on_one_device(ctx, G):
+    """ShardedEncodePQ's device steps for G row shards of one matrix: k-means on the gathered sample gives the same
+    centroids as the single-GPU encode with the same sample ids, and the code shards are byte slices of its codes"""
+    count, dim, chunk = 30_000, 64, 2
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev); g.manual_seed(5)
+    data = torch.rand((count, dim), generator=g, device=dev)
+    torch.cuda.synchronize()
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
+    whole = qz.EncodedVectorsPQ.encode_dev(data.data_ptr(), vp, chunk, ctx=ctx, seed=2)
+    ref = whole.download()
+    enc = S.ShardedEncodePQ(ctx, device=dev)
+    ids = S.sample_ids(count, S.KMEANS_SAMPLE, 2)
+    sample = data[torch.as_tensor(ids.astype(np.int64), device=dev)].contiguous()
+    torch.cuda.synchronize()
+    cen = enc._gpu_train(sample, chunk, 2)
+    assert np.array_equal(cen.view(np.uint32), whole.centroids.view(np.uint32)), "k-means on the gathered sample differs"
+    nch = dim // chunk
+    for r in range(G):
+        lo, hi = S.shard_range(count, r, G)
+        part = data[lo:hi].contiguous(); torch.cuda.synchronize()
+        ix = enc._gpu_assign(part, qz.VectorParameters(dim, hi - lo, qz.DistanceType.Dot, False), chunk, cen, lo)
+        assert np.array_equal(ix.download(), ref[lo * nch: hi * nch])

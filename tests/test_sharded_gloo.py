@@ -139,3 +139,40 @@ def test_sharded_encode_is_a_slice_of_the_global_encode(world, count, dim, quant
     out = mp.Manager().list([0] * world)
     mp.spawn(_encode_worker, args=(world, _free_port(), count, dim, quantile, out), nprocs=world, join=True)
     assert list(out) == [1] * world
+
+
+def _pq_encode_worker(rank, world, port, count, dim, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        data = O.uniform(42, count * dim).reshape(count, dim)
+        ids = np.sort(np.random.default_rng(5).permutation(count)[:300]).astype(np.uint64)
+        bounds = O.pq_division(dim, 2)
+        full = O.OraclePQ.encode(data, O.DOT, False, 2, sample_ids=ids)
+        lo, hi = S.shard_range(count, rank, world)
+        seen = {}
+
+        def train(sample, chunk_size, seed):  # stand-in for qz_pq_train_dev on the gathered sample
+            seen["sample_ok"] = np.array_equal(sample.numpy(), data[ids.astype(np.int64)])
+            return O.OraclePQ.find_centroids(sample.numpy(), bounds)
+
+        def assign(rows, vp_local, chunk_size, cen, id_base):  # stand-in for qz_pq_assign_dev
+            seen["id_base"] = id_base
+            return cen, O.OraclePQ.assign(rows.numpy(), bounds, cen)
+
+        from quantization_b200 import VectorParameters, DistanceType
+        enc = S.ShardedEncodePQ(None, local_train=train, local_assign=assign)
+        cen, codes = enc.encode(torch.from_numpy(data[lo:hi].copy()), VectorParameters(dim, count, DistanceType.Dot, False), 2, ids)
+        nch = dim // 2
+        ok = (seen["sample_ok"] and seen["id_base"] == lo and np.array_equal(cen, full.centroids)
+              and np.array_equal(codes, full.codes[lo * nch: hi * nch]))
+        out[rank] = int(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_pq_encode_gathers_the_sample_and_assigns_locally():
+    world = 2
+    out = mp.Manager().list([0] * world)
+    mp.spawn(_pq_encode_worker, args=(world, _free_port(), 700, 8, out), nprocs=world, join=True)
+    assert list(out) == [1] * world

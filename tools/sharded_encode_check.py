@@ -44,6 +44,27 @@ for quantile in (None, 0.99):
               f"{bool(flag.item())}; sharded encode of {hi - lo} rows/rank {ms:.2f} ms wall", flush=True)
     ok_all &= bool(flag.item())
     del data, whole, shard, mine
+# PQ: all-gather of the k-means sample, identical training on every rank, local assignment
+pcount, pdim = 100_000, 256
+g = torch.Generator(device=dev); g.manual_seed(7)
+data = torch.rand((pcount, pdim), generator=g, device=dev); torch.cuda.synchronize()
+vp = qz.VectorParameters(pdim, pcount, qz.DistanceType.Dot, False)
+whole = qz.EncodedVectorsPQ.encode_dev(data.data_ptr(), vp, 2, ctx=ctx, seed=3)
+lo, hi = S.shard_range(pcount, rank, world)
+mine = data[lo:hi].contiguous(); torch.cuda.synchronize()
+t0 = time.perf_counter()
+shard = S.ShardedEncodePQ(ctx, device=dev).encode(mine, vp, 2, seed=3)
+torch.cuda.synchronize(); ms = (time.perf_counter() - t0) * 1e3
+nch = pdim // 2
+same = np.array_equal(shard.download(), whole.download()[lo * nch: hi * nch]) and \
+    np.array_equal(shard.centroids.view(np.uint32), whole.centroids.view(np.uint32))
+flag = torch.tensor([int(same)], device=dev)
+if world > 1:
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+if rank == 0:
+    print(f"world {world} PQ {pcount} x {pdim} chunk 2: centroids bit-identical on every rank and code shards are slices of the "
+          f"single-GPU codes: {bool(flag.item())}; {ms:.1f} ms wall", flush=True)
+ok_all &= bool(flag.item())
 if world > 1:
     dist.destroy_process_group()
 sys.exit(0 if ok_all else 1)
