@@ -335,7 +335,8 @@ def run_gpu(args):
                              + ("exceeds" if rows * wl["row_bytes"] > 126e6 else "FITS IN") + " the 126 MB L2; no flush"},
             "e2e": {"value": total_rows * args.steps / (e2e_ms * 1e-3), "unit": "vectors/s",
                     "h2d_bytes_per_step": int(q_host.nbytes),
-                    "d2h_bytes_per_step": int(k * 8), "ms_per_step": e2e_ms / args.steps,
+                    "d2h_bytes_per_step": int((1024 + k) * 4),  # one copy: scores[QZ_MAX_K] + ids[k] are contiguous on the device
+                    "ms_per_step": e2e_ms / args.steps,
                     "call": ("qz_search_topk_peer" if use_peer else "qz_search_topk") +
                             " (host f32 query -> host scores, ids), one call per step"},
             "gpu_launches": int(launches),

@@ -152,16 +152,15 @@ qz_status qz_search_topk_peer(qz_index *ix, qz_peer *pe, const float *query, uin
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t fb_pad = (fb + 255) / 256 * 256, qb_pad = (qb + 255) / 256 * 256;
     QZ_TRY(ensure_query(ctx, fb_pad + qb_pad + 16));
-    QZ_TRY(ensure_pin(ctx, fb_pad + (size_t)k * 8));
+    QZ_TRY(ensure_pin(ctx, fb_pad + (size_t)2 * QZ_MAX_K * 4));
     uint8_t *d_f32 = ctx->d_query, *d_blob = ctx->d_query + fb_pad;
     memcpy(ctx->h_pin, query, fb);
     QZ_CUDA(ctx, cudaMemcpyAsync(d_f32, ctx->h_pin, fb, cudaMemcpyHostToDevice, ctx->stream));
     QZ_TRY(qz_encode_query_dev(ix, reinterpret_cast<const float *>(d_f32), 1, d_blob));
     QZ_TRY(qz_scan_topk_peer_dev(ix, pe, d_blob, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
     float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
-    uint32_t *hi = reinterpret_cast<uint32_t *>(ctx->h_pin + fb_pad + (size_t)k * 4);
-    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    QZ_CUDA(ctx, cudaMemcpyAsync(hi, ctx->d_ids_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + QZ_MAX_K);
+    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, ((size_t)QZ_MAX_K + k) * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     uint32_t m = 0;
     while (m < k && hi[m] != 0xFFFFFFFFu) m++;  // empty slots decode to id 0xFFFFFFFF

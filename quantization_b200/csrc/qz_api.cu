@@ -200,16 +200,15 @@ qz_status qz_scan_topk(qz_index *ix, const void *enc_query, uint32_t k, int32_t 
     const size_t qb = qz_query_bytes(ix), qb_pad = (qb + 255) / 256 * 256;
     if (qb && !enc_query) return fail(ctx, QZ_ARGUMENTS, "scan_topk: NULL query");
     QZ_TRY(ensure_query(ctx, qb_pad + 16));
-    QZ_TRY(ensure_pin(ctx, qb_pad + (size_t)k * 8));
+    QZ_TRY(ensure_pin(ctx, qb_pad + (size_t)2 * QZ_MAX_K * 4));
     if (qb) {
         memcpy(ctx->h_pin, enc_query, qb);
         QZ_CUDA(ctx, cudaMemcpyAsync(ctx->d_query, ctx->h_pin, qb, cudaMemcpyHostToDevice, ctx->stream));
     }
     QZ_TRY(qz_scan_topk_dev(ix, ctx->d_query, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
     float *hs = reinterpret_cast<float *>(ctx->h_pin + qb_pad);
-    uint32_t *hi = reinterpret_cast<uint32_t *>(ctx->h_pin + qb_pad + (size_t)k * 4);
-    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    QZ_CUDA(ctx, cudaMemcpyAsync(hi, ctx->d_ids_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + QZ_MAX_K);
+    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, ((size_t)QZ_MAX_K + k) * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const uint32_t m = (uint32_t)(ix->count < k ? ix->count : k);
     memcpy(scores, hs, (size_t)m * 4);
@@ -230,7 +229,7 @@ qz_status qz_search_topk(qz_index *ix, const float *query, uint32_t k, int32_t l
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t fb_pad = (fb + 255) / 256 * 256, qb_pad = (qb + 255) / 256 * 256;
     QZ_TRY(ensure_query(ctx, fb_pad + qb_pad + 16));
-    QZ_TRY(ensure_pin(ctx, fb_pad + (size_t)k * 8));
+    QZ_TRY(ensure_pin(ctx, fb_pad + (size_t)2 * QZ_MAX_K * 4));
     uint8_t *d_f32 = ctx->d_query, *d_blob = ctx->d_query + fb_pad;
     if (fb && qb) {
         memcpy(ctx->h_pin, query, fb);
@@ -239,9 +238,8 @@ qz_status qz_search_topk(qz_index *ix, const float *query, uint32_t k, int32_t l
     }
     QZ_TRY(qz_scan_topk_dev(ix, d_blob, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
     float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
-    uint32_t *hi = reinterpret_cast<uint32_t *>(ctx->h_pin + fb_pad + (size_t)k * 4);
-    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    QZ_CUDA(ctx, cudaMemcpyAsync(hi, ctx->d_ids_k, (size_t)k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + QZ_MAX_K);
+    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, ((size_t)QZ_MAX_K + k) * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const uint32_t m = (uint32_t)(ix->count < k ? ix->count : k);
     memcpy(scores, hs, (size_t)m * 4);

@@ -127,8 +127,9 @@ qz_status qz_ctx_create(int32_t device, void *stream, qz_ctx **out) {
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_done, 256);
     if (e == cudaSuccess) e = cudaMemset(ctx->d_done, 0, 256);
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_keys, QZ_MAX_K * sizeof(uint64_t));
-    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_scores_k, QZ_MAX_K * sizeof(float));
-    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_ids_k, QZ_MAX_K * sizeof(uint32_t));
+    // one allocation, ids right behind the scores: a host-facing search reads both back with ONE copy
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->d_scores_k, 2 * QZ_MAX_K * sizeof(float));
+    if (e == cudaSuccess) ctx->d_ids_k = reinterpret_cast<uint32_t *>(ctx->d_scores_k + QZ_MAX_K);
     if (e != cudaSuccess) {
         qz_status st = cuda_fail(nullptr, e, "qz_ctx_create");
         qz_ctx_destroy(ctx);
@@ -153,8 +154,7 @@ static void ctx_free(qz_ctx *ctx) {
     cudaFree(ctx->d_merge_tmp);
     cudaFree(ctx->d_done);
     cudaFree(ctx->d_keys);
-    cudaFree(ctx->d_scores_k);
-    cudaFree(ctx->d_ids_k);
+    cudaFree(ctx->d_scores_k);  // d_ids_k lives in the same allocation
     cudaFree(ctx->d_query);
     cudaFree(ctx->d_io);
     if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
