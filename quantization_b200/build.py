@@ -19,6 +19,12 @@ FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-Xcompiler", "-fPIC,-fvisibility=hidden,-O2", "--fmad=false", "-Xptxas", "-v",
 ]
+# QZ_TUNING=1: compile the experiment switches (QZ_SCAN_*, QZ_PQ_*, QZ_BATCH_* environment variables read by
+# csrc/qz_internal.h tune_u32 / tune_flag) into the library.  The default (production) build has none of them.
+TUNING = os.environ.get("QZ_TUNING", "") not in ("", "0")
+if TUNING:
+    FLAGS.append("-DQZ_TUNING")
+STAMP = os.path.join(OBJ, "flags.stamp")
 
 
 def _deps():
@@ -27,8 +33,15 @@ def _deps():
     return out
 
 
+def _stamp_matches():
+    try:
+        return open(STAMP).read() == " ".join(FLAGS)
+    except OSError:
+        return False
+
+
 def needs_build():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not _stamp_matches():
         return True
     t = os.path.getmtime(LIB)
     return any(os.path.getmtime(p) > t for p in _deps())
@@ -57,12 +70,16 @@ def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB
     os.makedirs(OBJ, exist_ok=True)
+    if not _stamp_matches():  # objects built with other flags (e.g. a QZ_TUNING build) are not reused
+        force = True
     with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
         objs = list(ex.map(lambda f: _compile(f, force), SOURCES))
     r = subprocess.run([NVCC, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
                         "-cudart", "shared", "-Xlinker", "-rpath,/usr/local/cuda/lib64"], capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    with open(STAMP, "w") as f:
+        f.write(" ".join(FLAGS))
     if verbose:
         for o in objs:
             print(open(o + ".log").read())

@@ -213,12 +213,7 @@ qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, 
                   uint32_t *Kp_out, const ScanFinal *fin) {
     if (fin) *fin->fused = false;
     qz_ctx *ctx = ix->ctx;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(pq_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSliceFloats * 4);
-        if (e != cudaSuccess) return cuda_fail(ctx, e, "pq attr");
-        attr_done = true;
-    }
+    QZ_TRY(ensure_smem_attr(ctx, (const void *)pq_scan_kernel, kSliceFloats * 4));
     const uint32_t slices = ix->pq_slices;
     if (slices == 0) {  // dim 0: every score is the empty sum
         QZ_TRY(ensure_io(ctx, ix->count * sizeof(float)));
@@ -231,7 +226,7 @@ qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, 
     QZ_TRY(check_launch(ctx, "pq_lut_permute_kernel"));
     // streaming kernel (pq_scan2.cu): k <= 128 is reduced inside the kernel; otherwise the final scores go to
     // partial[0] and the generic top-k pass runs over that one part
-    static const bool env_v1 = getenv("QZ_PQ_V1") != nullptr;
+    const bool env_v1 = tune_flag("QZ_PQ_V1");
     if (!env_v1) {
         const bool fused = k > 0 && k <= 128;
         float *sc = fused ? d_scores : (d_scores ? d_scores : ix->d_pq_partial);

@@ -261,11 +261,9 @@ bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32
                      const ScanFinal *fin, cudaError_t *err) {
     *err = cudaSuccess;
     if (n_chunks % 16 != 0 || count == 0 || count > 0x7FFFFFFFull) return false;
-    static bool attr_done = false;
-    if (!attr_done) {
-        *err = cudaFuncSetAttribute(pq_scan2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)227 * 1024);
-        if (*err != cudaSuccess) return true;
-        attr_done = true;
+    if (ensure_smem_attr(ctx, (const void *)pq_scan2_kernel, 227 * 1024) != QZ_OK) {
+        *err = cudaErrorInvalidValue;
+        return true;
     }
     CUtensorMap map;
     if (!make_tensor_map_u8_2d(&map, d_codes, count, n_chunks, kPq2SliceChunks, kPq2TileRows, CU_TENSOR_MAP_SWIZZLE_NONE,
@@ -280,8 +278,7 @@ bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32
     p.k = k ? k : 1;
     p.flip = largest ? 0u : 0xFFFFFFFFu;
     p.id_base = id_base;
-    static const uint32_t env_slots = getenv("QZ_PQ_SLOTS") ? atoi(getenv("QZ_PQ_SLOTS")) : 0;
-    static const uint32_t env_block = getenv("QZ_PQ_BLOCK_ROWS") ? atoi(getenv("QZ_PQ_BLOCK_ROWS")) : 0;
+    const uint32_t env_slots = tune_u32("QZ_PQ_SLOTS", 0), env_block = tune_u32("QZ_PQ_BLOCK_ROWS", 0);
     // n_slots must be a multiple of the group count: a slot then always serves the same warp group, so no waiter
     // can be two phases ahead of a slot's mbarrier (with 6 slots a fast group passed the parity wait of a tile two
     // fills ahead while the other group's fill was still in flight: launch failure, mbarrier over-arrival)
@@ -300,7 +297,7 @@ bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32
     const uint32_t grid = p.n_blocks < (uint32_t)ctx->sm_count ? p.n_blocks : (uint32_t)ctx->sm_count;
     const size_t smem = fixed + (size_t)p.block_rows * 4;
     if (fin) *fin->fused = false;
-    if (fin && k && grid <= kPruneMaxLists && !getenv("QZ_SCAN_NO_FUSED_MERGE")) {
+    if (fin && k && grid <= kPruneMaxLists && !tune_flag("QZ_SCAN_NO_FUSED_MERGE")) {
         MergeParams &m = p.merge;
         m.in = ctx->d_partial;
         m.n_lists = grid;

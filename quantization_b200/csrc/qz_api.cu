@@ -103,6 +103,7 @@ qz_status qz_u8_index_set_params(qz_index *ix, float alpha, float offset, float 
     ix->alpha = alpha;
     ix->offset = offset;
     ix->multiplier = multiplier;
+    ix->soa_valid = false;  // the batched path's mirror (built from the storage and the multiplier) is stale
     return QZ_OK;
 }
 
@@ -116,6 +117,7 @@ void qz_index_destroy(qz_index *ix) {
             cudaFree(ix->d_storage);
             cudaFree(ix->d_codes_soa);
             cudaFree(ix->d_voff_soa);
+            cudaFree(ix->d_vq_soa);
             cudaFree(ix->d_batch);
             pq_index_free(ix);
         }

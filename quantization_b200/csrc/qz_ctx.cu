@@ -49,6 +49,15 @@ qz_status ensure_pin(qz_ctx *ctx, size_t bytes) {
     return QZ_OK;
 }
 
+qz_status ensure_smem_attr(qz_ctx *ctx, const void *fn, int bytes) {
+    std::lock_guard<std::mutex> g(ctx->attr_mu);
+    if (ctx->attr_done.count(fn)) return QZ_OK;
+    QZ_CUDA(ctx, cudaSetDevice(ctx->device));
+    QZ_CUDA(ctx, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    ctx->attr_done.insert(fn);
+    return QZ_OK;
+}
+
 static void timing_drain(qz_ctx *ctx, bool wait) {
     while (ctx->ev_tail < ctx->ev_head) {
         const int i = (int)(ctx->ev_tail % qz_ctx::kTimingRing);

@@ -6,6 +6,7 @@
 #include <atomic>
 #include <mutex>
 #include <string>
+#include <unordered_set>
 
 #include "../../include/qz_cuda.h"
 
@@ -41,6 +42,13 @@ struct qz_ctx {
     uint64_t ev_head = 0, ev_tail = 0;  // [tail, head) pairs are recorded and not yet read
     double timed_ms = 0.0;
     uint64_t timed_n = 0;
+    // One-time kernel attribute setup.  cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies to the CURRENT
+    // device only, so "done" is a property of the context (= device), never of the process: a host that creates
+    // contexts on several devices needs the attribute on each of them (qz::ensure_smem_attr).
+    std::mutex attr_mu;
+    std::unordered_set<const void *> attr_done;
+    int batch_cl_pick = 0;                     // u8_batch.cu: cluster size chosen for this device, 0 = not yet
+    int batch_cl_grid[3] = {0, 0, 0};          // resident CTAs for cluster size 1 / 2
 };
 
 struct qz_index {
@@ -59,6 +67,9 @@ struct qz_index {
     // batched tensor-core path (u8_batch.cu): SoA mirror + per-batch scratch, built lazily
     uint8_t *d_codes_soa = nullptr;  // [count][actual_dim]
     float *d_voff_soa = nullptr;     // [count]
+    int32_t *d_vq_soa = nullptr;     // [count] floor(vector offset / multiplier) (integer filter of the batched path)
+    bool soa_valid = false;          // the mirror matches the storage and the Metadata scalars
+    bool vq_ok = false;              // d_vq_soa is usable (finite non-zero multiplier, offsets in range)
     float voff_absmax = 0.0f;        // max |vector offset| (bound used by the batched fast filter)
     uint8_t *d_batch = nullptr;      // scratch arena for one batch call
     size_t batch_bytes = 0;
@@ -82,6 +93,8 @@ qz_status cuda_fail(qz_ctx *ctx, cudaError_t e, const char *what);
 qz_status ensure_query(qz_ctx *ctx, size_t bytes);
 qz_status ensure_io(qz_ctx *ctx, size_t bytes);
 qz_status ensure_pin(qz_ctx *ctx, size_t bytes);
+// opt the kernel `fn` into `bytes` of dynamic shared memory on this context's device, once per context
+qz_status ensure_smem_attr(qz_ctx *ctx, const void *fn, int bytes);
 // bracket the dominant kernel of a scan with events when timing is on
 void timing_begin(qz_ctx *ctx);
 void timing_end(qz_ctx *ctx);
@@ -97,6 +110,21 @@ void timing_end(qz_ctx *ctx);
         qz_status s__ = (call);        \
         if (s__ != QZ_OK) return s__;  \
     } while (0)
+
+// Experiment switches (tile sizes, ring depth, schedules ...) exist only in builds made with -DQZ_TUNING
+// (QZ_TUNING=1 python -m quantization_b200.build, used by the sweeps under tools/); a production build ignores
+// the environment entirely.
+#ifdef QZ_TUNING
+#include <stdlib.h>
+static inline uint32_t tune_u32(const char *name, uint32_t dflt) {
+    const char *e = getenv(name);
+    return e ? (uint32_t)atoi(e) : dflt;
+}
+static inline bool tune_flag(const char *name) { return getenv(name) != nullptr; }
+#else
+static inline uint32_t tune_u32(const char *, uint32_t dflt) { return dflt; }
+static inline bool tune_flag(const char *) { return false; }
+#endif
 
 static inline uint32_t pow2_ceil(uint32_t v) {
     uint32_t p = 1;

@@ -14,10 +14,10 @@ struct ScanPlan {
     size_t smem;
 };
 
-cudaError_t launch_row_scan_dot(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
-cudaError_t launch_row_scan_l1(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
-cudaError_t launch_row_scan_xor(uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
-cudaError_t launch_row_scan_xorv(uint32_t, uint32_t, bool, const RowScanParams &, uint32_t, size_t, cudaStream_t);
+cudaError_t launch_row_scan_dot(qz_ctx *, uint32_t, bool, const RowScanParams &, uint32_t, size_t);
+cudaError_t launch_row_scan_l1(qz_ctx *, uint32_t, bool, const RowScanParams &, uint32_t, size_t);
+cudaError_t launch_row_scan_xor(qz_ctx *, uint32_t, bool, const RowScanParams &, uint32_t, size_t);
+cudaError_t launch_row_scan_xorv(qz_ctx *, uint32_t, uint32_t, bool, const RowScanParams &, uint32_t, size_t);
 
 static const int kWplSet[] = {1, 2, 3, 4, 6, 8, 12, 16, 24, 32};
 
@@ -32,10 +32,8 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
                           bool small_rows, ScanPlan *pl) {
     if (row_bytes == 0 || row_bytes % 4 != 0 || code_words == 0 || code_words > 32 * 32) return false;
     if (count >= 0xFFFFFFFFull) return false;
-    static const uint32_t env_target = getenv("QZ_SCAN_TILE_BYTES") ? atoi(getenv("QZ_SCAN_TILE_BYTES")) : 0;
-    static const uint32_t env_align = getenv("QZ_SCAN_ROW_ALIGN") ? atoi(getenv("QZ_SCAN_ROW_ALIGN")) : 0;
-    static const uint32_t env_slots = getenv("QZ_SCAN_SLOTS") ? atoi(getenv("QZ_SCAN_SLOTS")) : 0;
-    static const uint32_t env_groups = getenv("QZ_SCAN_GROUPS") ? atoi(getenv("QZ_SCAN_GROUPS")) : 0;
+    const uint32_t env_target = tune_u32("QZ_SCAN_TILE_BYTES", 0), env_align = tune_u32("QZ_SCAN_ROW_ALIGN", 0);
+    const uint32_t env_slots = tune_u32("QZ_SCAN_SLOTS", 0), env_groups = tune_u32("QZ_SCAN_GROUPS", 0);
     const uint32_t target = env_target ? env_target : (small_rows ? 12416 : 24832);
     const uint32_t align = env_align ? env_align : kTileRowAlign;
     uint32_t tile_rows = (target / row_bytes) / align * align;
@@ -53,7 +51,7 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
     uint32_t n_groups = env_groups ? pow2_ceil(env_groups) : 8;
     if (n_groups > (uint32_t)kConsumerWarps) n_groups = kConsumerWarps;
     if (n_groups > n_slots) n_groups = n_slots;
-    pl->vec = small_rows && row_bytes % 16 == 0 && row_bytes <= 512 && !getenv("QZ_SCAN_NO_VEC");
+    pl->vec = small_rows && row_bytes % 16 == 0 && row_bytes <= 512 && !tune_flag("QZ_SCAN_NO_VEC");
     pl->lpr = 8;
     uint32_t need = (code_words + 31) / 32;
     uint32_t wpl = 0;
@@ -68,7 +66,7 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
     if (pl->vec) {
         const uint32_t row_vec = row_bytes / 16;
         // 4 lanes per row when two consecutive rows then fall into disjoint bank halves (stride = 64 mod 128 bytes)
-        static const uint32_t env_lpr = getenv("QZ_SCAN_LPR") ? atoi(getenv("QZ_SCAN_LPR")) : 0;
+        const uint32_t env_lpr = tune_u32("QZ_SCAN_LPR", 0);
         pl->lpr = env_lpr ? env_lpr : ((row_vec % 8 == 4 && row_vec <= 16) ? 4 : 8);
         wpl = (row_vec + pl->lpr - 1) / pl->lpr;  // 16-byte vectors per lane
         pl->full = row_vec == pl->lpr * wpl;
@@ -120,7 +118,7 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     p.n_groups = pl.n_groups;
     // u8 CTAs see a few thousand rows: 512 unfiltered rows buy a threshold good enough that no warp ever fills its
     // staging buffer.  Binary CTAs see ~70k rows: a longer warm-up keeps the buffers from filling all at once.
-    static const uint32_t env_warm = getenv("QZ_SCAN_WARM") ? atoi(getenv("QZ_SCAN_WARM")) : 0;
+    const uint32_t env_warm = tune_u32("QZ_SCAN_WARM", 0);
     p.warm_rows = env_warm ? env_warm : (ix->codec == QZ_CODEC_BIN ? 2048 : 512);
     p.n_tiles = pl.n_tiles;
     p.query = reinterpret_cast<const uint32_t *>(d_query);
@@ -136,7 +134,7 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     p.id_base = ix->id_base;
     uint32_t grid = pl.n_tiles < (uint32_t)ctx->sm_count ? pl.n_tiles : (uint32_t)ctx->sm_count;
     if (fin) *fin->fused = false;
-    static const bool env_nofuse = getenv("QZ_SCAN_NO_FUSED_MERGE") != nullptr;
+    const bool env_nofuse = tune_flag("QZ_SCAN_NO_FUSED_MERGE");
     if (fin && k && !env_nofuse && grid <= kPruneMaxLists) {
         const uint32_t lpc = pow2_ceil(grid < 2 ? 2 : grid);
         size_t need = (size_t)(lpc / 2) * Kp * 8;
@@ -172,11 +170,13 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
         return fail(ctx, QZ_ARGUMENTS, "peer exchange needs the in-launch merge (k <= 128, streaming row shape)");
     cudaError_t e;
     timing_begin(ctx);
-    if (ix->codec == QZ_CODEC_BIN && pl.vec) e = launch_row_scan_xorv(pl.lpr, pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
-    else if (ix->codec == QZ_CODEC_BIN) e = launch_row_scan_xor(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
-    else if (ix->distance == QZ_L1) e = launch_row_scan_l1(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
-    else e = launch_row_scan_dot(pl.wpl, pl.full, p, grid, pl.smem, ctx->stream);
+    if (ix->codec == QZ_CODEC_BIN && pl.vec) e = launch_row_scan_xorv(ctx, pl.lpr, pl.wpl, pl.full, p, grid, pl.smem);
+    else if (ix->codec == QZ_CODEC_BIN) e = launch_row_scan_xor(ctx, pl.wpl, pl.full, p, grid, pl.smem);
+    else if (ix->distance == QZ_L1) e = launch_row_scan_l1(ctx, pl.wpl, pl.full, p, grid, pl.smem);
+    else e = launch_row_scan_dot(ctx, pl.wpl, pl.full, p, grid, pl.smem);
     timing_end(ctx);
+    if (e == cudaErrorInvalidValue && !ctx->err.empty() && ctx->err.find("cudaFuncSetAttribute") != std::string::npos)
+        return QZ_ENCODING;  // ensure_smem_attr failed and left its message
     if (e != cudaSuccess) return cuda_fail(ctx, e, "row_scan_kernel launch");
     ctx->launches++;
     if (n_lists) *n_lists = grid;
@@ -188,15 +188,8 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
 // memory (<= 32768/Kp lists), otherwise a tree of launches through ctx->d_merge_tmp.
 qz_status launch_merge(qz_ctx *ctx, const uint64_t *d_in, uint32_t n_lists, uint32_t in_len, uint32_t in_stride,
                        uint32_t k, int largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e =
-            cudaFuncSetAttribute(merge_lists_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(prune_merge_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
-        if (e != cudaSuccess) return cuda_fail(ctx, e, "merge attr");
-        attr_done = true;
-    }
+    QZ_TRY(ensure_smem_attr(ctx, (const void *)merge_lists_kernel<0>, 128 * 1024));
+    QZ_TRY(ensure_smem_attr(ctx, (const void *)prune_merge_kernel<0>, 128 * 1024));
     const uint32_t Kp = topk_pad(in_len > k ? in_len : k);
     const uint32_t max_lists = 32768 / Kp;  // (lists/2)*Kp keys <= 16384
     const uint64_t *in = d_in;

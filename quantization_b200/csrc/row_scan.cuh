@@ -359,7 +359,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
                 *lock = prev == gridDim.x - 1;
             }
             named_bar_sync(1, kConsumerWarps * 32);
-            if (*lock) {
+            // (the merge's work area starts at shared offset 0 and may overlay `lock` when the ring is small:
+            // everyone reads the flag into a register before anyone enters the merge)
+            const int is_last = *lock;
+            named_bar_sync(1, kConsumerWarps * 32);
+            if (is_last) {
                 prune_merge<1, true>(p.merge, reinterpret_cast<uint64_t *>(ring), threadIdx.x, kConsumerWarps * 32);
                 if (threadIdx.x == 0) *p.done = 0;
                 if (p.px.world > 1) peer_exchange_merge(p.px, p.k, reinterpret_cast<uint64_t *>(ring));

@@ -1,31 +1,26 @@
 // row_scan_inst.cuh — template dispatch of row_scan_kernel for one OP (included by
 // row_scan_{dot,l1,xor}.cu so the three families compile in parallel).
 #pragma once
+#include "qz_internal.h"
 #include "row_scan.cuh"
 
 namespace qz {
 
 template <int OP, int WPL, bool FULL>
-static cudaError_t launch_one(const RowScanParams &p, uint32_t grid, size_t smem, cudaStream_t stream) {
-    static bool attr_done = false;  // per instantiation
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(row_scan_kernel<OP, WPL, FULL>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)227 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
-    row_scan_kernel<OP, WPL, FULL><<<grid, kScanThreads, smem, stream>>>(p);
+static cudaError_t launch_one(qz_ctx *ctx, const RowScanParams &p, uint32_t grid, size_t smem) {
+    if (ensure_smem_attr(ctx, (const void *)row_scan_kernel<OP, WPL, FULL>, 227 * 1024) != QZ_OK)
+        return cudaErrorInvalidValue;  // (text already in ctx->err)
+    row_scan_kernel<OP, WPL, FULL><<<grid, kScanThreads, smem, ctx->stream>>>(p);
     return cudaGetLastError();
 }
 
 // wpl must come from row_scan_wpl(); `full` = code_words == 32 * wpl
 template <int OP>
-static cudaError_t launch_wpl(uint32_t wpl, bool full, const RowScanParams &p, uint32_t grid, size_t smem,
-                              cudaStream_t s) {
+static cudaError_t launch_wpl(qz_ctx *s, uint32_t wpl, bool full, const RowScanParams &p, uint32_t grid, size_t smem) {
 #define QZ_WPL_CASE(W)                                             \
     case W:                                                        \
-        return full ? launch_one<OP, W, true>(p, grid, smem, s)    \
-                    : launch_one<OP, W, false>(p, grid, smem, s);
+        return full ? launch_one<OP, W, true>(s, p, grid, smem)    \
+                    : launch_one<OP, W, false>(s, p, grid, smem);
     switch (wpl) {
         QZ_WPL_CASE(1)
         QZ_WPL_CASE(2)
@@ -37,7 +32,7 @@ static cudaError_t launch_wpl(uint32_t wpl, bool full, const RowScanParams &p, u
         QZ_WPL_CASE(16)
         QZ_WPL_CASE(24)
         default:
-            return full ? launch_one<OP, 32, true>(p, grid, smem, s) : launch_one<OP, 32, false>(p, grid, smem, s);
+            return full ? launch_one<OP, 32, true>(s, p, grid, smem) : launch_one<OP, 32, false>(s, p, grid, smem);
     }
 #undef QZ_WPL_CASE
 }

@@ -10,9 +10,10 @@
 //               128-query x 128-byte A block and a 256-row x 128-byte B block per pipeline stage
 //   warp 1      MMA issuer: tcgen05.mma.cta_group::1.kind::i8, u8 x u8 -> s32, M=128 N=256 K=32 per
 //               instruction, accumulators in TMEM (2 buffers x 256 columns), tcgen05.commit frees stages
-//   warps 2..9  epilogue: tcgen05.ld (thread = TMEM lane = one query), affine map, threshold filter
-//               against the query's current k-th best key, survivors appended to the query's
-//               candidate buffer in global memory
+//   warps 2..9  epilogue: tcgen05.ld (thread = TMEM lane = one query), threshold filter in the INTEGER domain
+//               (one VIADDMNMX per accumulator against a per-query integer bound, see u8_batch.cu), exact
+//               re-score of the few survivors in the reference's f32 order, survivors appended to the
+//               query's candidate buffer in global memory
 // Operands come from a device-side SoA mirror (codes[N][K] contiguous, offsets[N]) because the
 // reference's AoS stride actual_dim + 4 is not a multiple of 16 bytes and cannot be a TMA stride.
 #pragma once
@@ -26,27 +27,33 @@ constexpr int kBatchM = 128;       // queries per tile (TMEM lanes)
 constexpr int kBatchN = 256;       // corpus rows per tile (TMEM columns per accumulator buffer)
 constexpr int kBatchKC = 128;      // code bytes per pipeline stage = one 128-byte swizzle row
 constexpr int kBatchStages = 4;
+constexpr int kEpiWarps = 8;       // epilogue warps: 2 per TMEM lane quarter, 128 accumulator columns each
 constexpr int kQueueCap = 256;     // candidates an epilogue warp can stage in shared memory between flushes
 constexpr int kVoffBufs = 4;       // ring of per-tile vector-offset blocks (1 KB each)
-constexpr int kBatchThreads = 320;  // producer, MMA, 8 epilogue warps
+constexpr int kBatchThreads = (2 + kEpiWarps) * 32;  // producer, MMA, epilogue warps
 constexpr uint32_t kStageA = kBatchM * kBatchKC;  // 16 KB
 constexpr uint32_t kStageB = kBatchN * kBatchKC;  // 32 KB
 constexpr uint32_t kStageBytes = kStageA + kStageB;
-constexpr size_t kBatchSmem = (size_t)kBatchStages * kStageBytes + kVoffBufs * kBatchN * 4 + 256 + 1024 + 8 * kQueueCap * 12;  // + voff ring, barriers, align slack, queues, barriers, align slack
+// stages + ring of per-tile vector offsets (f32) and their integer images (s32) + barriers + align slack + queues
+constexpr size_t kBatchSmem = (size_t)kBatchStages * kStageBytes + 2 * kVoffBufs * kBatchN * 4 + 256 + 1024 + kEpiWarps * kQueueCap * 12;
 
 struct U8BatchParams {
     uint32_t nq, k_chunks;       // queries; ceil(actual_dim / 128)
     uint32_t row_begin, row_end; // corpus rows of this launch (chunk)
     uint32_t n_qb, n_ct;         // query blocks, corpus tiles in the chunk
     const float *qoff;           // [nq]
-    const float *voff;           // [count]
-    float multiplier, voff_absmax;  // voff_absmax = max |vector offset| over the index
+    const float *voff;           // [count] vector offsets
+    const int32_t *vq;           // [count] floor(vector offset / multiplier): the offsets in units of one integer step
+    float multiplier, rmult;     // rmult = 1 / multiplier (integer filter only)
+    float voff_absmax;           // max |vector offset| over the index
     uint32_t id_base, flip, cap;
     const uint64_t *thr;         // [nq] current k-th best key (0 = none yet)
     uint64_t *cand;              // [nq][cap]
     uint32_t *cnt;               // [nq]
     uint32_t *overflow;          // set when a candidate did not fit
-    uint32_t dbg;                // experiment switches (0 in production)
+#ifdef QZ_TUNING
+    uint32_t dbg;                // experiment switches (tuning builds only): 1 = no filtering at all, 2 = no re-scoring
+#endif
 };
 
 // bounded spin: a pipeline bug traps (launch failure) instead of hanging the device
@@ -86,6 +93,27 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_
         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}" ::"r"(tmem_d),
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u)
         : "memory");
+}
+// the same MMA with the descriptors given as their low words (start address, the only part that changes between
+// stages and K steps) and one shared high word: a 32-bit add per instruction in the single issuing thread
+__device__ __forceinline__ void umma_i8_lo(uint32_t tmem_d, uint32_t adesc_lo, uint32_t bdesc_lo, uint32_t desc_hi,
+                                           uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %4, {%6, %6, %6, %6}, p;\n\t}" ::"r"(tmem_d),
+        "r"(adesc_lo), "r"(bdesc_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate), "r"(0u)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t umma_desc_sw128_lo(const void *smem_ptr) {
+    return ((smem_u32(smem_ptr) & 0x3FFFFu) >> 4) | (1u << 16);
+}
+constexpr uint32_t kUmmaDescSw128Hi = (1024u >> 4) | (1u << 14) | (2u << 29);  // SBO 1024 B, version 1, SWIZZLE_128B
+// one lane of a converged warp (always the same one for the full mask)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -143,12 +171,6 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[3
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr));
 }
-// one accumulator (this lane's row, one column); waits for every outstanding tcgen05.ld of the thread
-__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
-    uint32_t v;
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\ttcgen05.wait::ld.sync.aligned;" : "=r"(v) : "r"(taddr) : "memory");
-    return v;
-}
 // the registers are tied to the wait so that no use of them can be scheduled above it
 __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;"
@@ -158,6 +180,14 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
                    "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
                  :
                  : "memory");
+}
+
+// wait for three outstanding 32-column loads; all 96 registers are tied to the wait
+__device__ __forceinline__ void tmem_ld_wait3(uint32_t (&a)[32], uint32_t (&b)[32], uint32_t (&c)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    tmem_ld_wait(a);  // (nothing is outstanding any more: these only pin the registers behind the wait)
+    tmem_ld_wait(b);
+    tmem_ld_wait(c);
 }
 
 }  // namespace qz
