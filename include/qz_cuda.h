@@ -67,6 +67,9 @@ QZ_API const char *qz_last_error(const qz_ctx *ctx);
 /* text of a failure that happened before a context existed (qz_ctx_create itself) */
 QZ_API const char *qz_last_global_error(void);
 QZ_API qz_status qz_ctx_synchronize(qz_ctx *ctx);
+/* the cudaStream_t every `*_dev` entry point of this context enqueues on (the caller's, or the one created by
+ * qz_ctx_create): a caller that mixes its own streams with `*_dev` calls orders them against this one with events */
+QZ_API void *qz_ctx_stream(const qz_ctx *ctx);
 /* number of kernels of this library launched through `ctx` so far (bench's gpu_launches) */
 QZ_API uint64_t qz_ctx_launch_count(const qz_ctx *ctx);
 QZ_API int32_t qz_ctx_sm_count(const qz_ctx *ctx);

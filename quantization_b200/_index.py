@@ -126,6 +126,13 @@ class DeviceIndex:
     def storage_dev(self):
         return int(self._L.qz_index_storage_dev(self.handle) or 0)
 
+    def host_storage(self):
+        """the flat encoded bytes on the host (EncodedStorage): the caller's array when the index was made from one,
+        else (device-side encode, sharded encode) a copy fetched from the device once and kept"""
+        if self.encoded_vectors is None:
+            self.encoded_vectors = self.download()
+        return np.ascontiguousarray(self.encoded_vectors, np.uint8).reshape(-1)
+
     def download(self):
         out = np.empty(self.count * self.row_bytes, np.uint8)
         if out.size:

@@ -22,6 +22,7 @@ _SIGS = {
     "qz_last_error": (C.c_char_p, [vp]),
     "qz_last_global_error": (C.c_char_p, []),
     "qz_ctx_synchronize": (C.c_int32, [vp]),
+    "qz_ctx_stream": (vp, [vp]),
     "qz_ctx_launch_count": (C.c_uint64, [vp]),
     "qz_ctx_sm_count": (C.c_int32, [vp]),
     "qz_ctx_set_timing": (C.c_int32, [vp, C.c_int32]),

@@ -5,6 +5,9 @@
 // resident ones, untouched.
 #include <string.h>
 
+#include <algorithm>
+#include <string>
+
 #include "qz_internal.h"
 
 using namespace qz;
@@ -46,7 +49,14 @@ qz_status qz_scan_topk_chunked(qz_index *a, qz_index *b, const uint8_t *host_sto
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const uint64_t cap = a->count, row = a->row_bytes;
     const uint64_t n_chunks = (count + cap - 1) / cap;
-    if (n_chunks > 32768) return fail(ctx, QZ_ARGUMENTS, "scan_topk_chunked: more than 32768 chunks; use bigger buffers");
+    {   // launch_merge reduces the per-chunk lists through ctx->d_merge_tmp (two halves of 128 * QZ_MAX_K keys): the
+        // first tree level leaves ceil(n_chunks / (32768 / Kp)) lists of Kp keys there
+        const uint64_t Kp = topk_pad(k), per_cta = 32768 / Kp;
+        const uint64_t max_chunks = std::min<uint64_t>(32768, per_cta * ((128ull * QZ_MAX_K) / Kp));
+        if (n_chunks > max_chunks)
+            return fail(ctx, QZ_ARGUMENTS, "scan_topk_chunked: too many chunks for this k (" + std::to_string(n_chunks) +
+                                               " > " + std::to_string(max_chunks) + "); use bigger buffers");
+    }
     const size_t qb_pad = (qb + 255) / 256 * 256;
     QZ_TRY(ensure_query(ctx, qb_pad + 16));
     QZ_TRY(ensure_pin(ctx, qb_pad > (size_t)k * 8 ? qb_pad : (size_t)k * 8));

@@ -102,8 +102,13 @@ qz_status bin_encode_rows(qz_ctx *ctx, const float *d_data, uint64_t count, uint
 // global min / max with the reference's strict-compare fold (NaN never wins), quantile.rs:5-19.
 // mm[0] = ordered bits of min (init order(FLT_MAX)), mm[1] = ordered bits of max (init order(-FLT_MAX))
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) minmax_kernel(const float *data, uint64_t n, uint32_t *mm) {
+// mm[0] / mm[1]: min / max as order bits; mm[2..3]: (u64) flat index of the FIRST element equal to zero (either sign),
+// ~0 when there is none.  The reference folds with strict < and > (quantile.rs:5-19), so when the minimum (maximum)
+// is a zero and zeros of both signs occur, it keeps the zero it saw first; order bits alone would always say -0.0
+// (+0.0).  The host resolves the sign from that element (fix_zero_sign).  `base` = flat index of data[0].
+__global__ void __launch_bounds__(256) minmax_kernel(const float *data, uint64_t n, uint64_t base, uint32_t *mm) {
     float lo = FLT_MAX, hi = -FLT_MAX;
+    unsigned long long zi = ~0ull;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t n4 = (((uintptr_t)data & 15) == 0) ? n / 4 : 0;
@@ -112,19 +117,25 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float *data, uint64_t
         const float4 v = d4[i];
         lo = fminf(lo, fminf(fminf(v.x, v.y), fminf(v.z, v.w)));
         hi = fmaxf(hi, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
+        if (zi == ~0ull && (v.x == 0.0f || v.y == 0.0f || v.z == 0.0f || v.w == 0.0f))  // (indices only grow: first hit)
+            zi = 4 * i + (v.x == 0.0f ? 0 : (v.y == 0.0f ? 1 : (v.z == 0.0f ? 2 : 3)));
     }
     for (uint64_t i = n4 * 4 + tid; i < n; i += stride) {
         lo = fminf(lo, data[i]);
         hi = fmaxf(hi, data[i]);
+        if (data[i] == 0.0f && i < zi) zi = i;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
         hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        const unsigned long long z2 = __shfl_xor_sync(0xffffffffu, zi, o);
+        zi = z2 < zi ? z2 : zi;
     }
     if ((threadIdx.x & 31) == 0) {
         atomicMin(&mm[0], f32_order_bits(__float_as_uint(lo)));
         atomicMax(&mm[1], f32_order_bits(__float_as_uint(hi)));
+        if (zi != ~0ull) atomicMin(reinterpret_cast<unsigned long long *>(mm + 2), zi + base);
     }
 }
 
@@ -331,26 +342,35 @@ static uint32_t grid_for(qz_ctx *ctx, uint64_t items, uint32_t per_block, uint32
     return b ? (uint32_t)b : 1u;
 }
 
-// min / max of a device array -> host floats
-qz_status dev_minmax(qz_ctx *ctx, const float *d_data, uint64_t n, uint32_t *d_mm, bool init) {
+// min / max of a device array -> host floats.  `base` = flat index of d_data[0] within the whole corpus (the host
+// encode streams the corpus through the device in pieces); *zero_idx = flat index of the first zero, ~0 if none.
+qz_status dev_minmax(qz_ctx *ctx, const float *d_data, uint64_t n, uint32_t *d_mm, bool init, uint64_t base) {
     if (init) {
-        uint32_t h[2] = {f32_order_bits(0x7F7FFFFFu), f32_order_bits(0xFF7FFFFFu)};  // FLT_MAX, -FLT_MAX
+        uint32_t h[4] = {f32_order_bits(0x7F7FFFFFu), f32_order_bits(0xFF7FFFFFu), 0xFFFFFFFFu, 0xFFFFFFFFu};  // FLT_MAX, -FLT_MAX, ~0
         QZ_CUDA(ctx, cudaMemcpyAsync(d_mm, h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream));
         QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // h is a stack temporary
     }
     if (n == 0) return QZ_OK;
-    minmax_kernel<<<grid_for(ctx, n, 256 * 16, 8), 256, 0, ctx->stream>>>(d_data, n, d_mm);
+    minmax_kernel<<<grid_for(ctx, n, 256 * 16, 8), 256, 0, ctx->stream>>>(d_data, n, base, d_mm);
     return launched(ctx, "minmax_kernel");
 }
 
-qz_status read_minmax(qz_ctx *ctx, const uint32_t *d_mm, float *mn, float *mx) {
-    uint32_t h[2];
+qz_status read_minmax(qz_ctx *ctx, const uint32_t *d_mm, float *mn, float *mx, uint64_t *zero_idx) {
+    uint32_t h[4];
     QZ_CUDA(ctx, cudaMemcpyAsync(h, d_mm, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     uint32_t a = f32_from_order_bits(h[0]), b = f32_from_order_bits(h[1]);
     memcpy(mn, &a, 4);
     memcpy(mx, &b, 4);
+    if (zero_idx) *zero_idx = ((uint64_t)h[3] << 32) | h[2];
     return QZ_OK;
+}
+
+// find_min_max_from_iter keeps the first zero it meets when the extreme is a zero (strict comparisons): give a zero
+// minimum / maximum the sign of the corpus' first zero element
+void fix_zero_sign(float *mn, float *mx, float first_zero) {
+    if (*mn == 0.0f) *mn = first_zero;
+    if (*mx == 0.0f) *mx = first_zero;
 }
 
 // the values at ascending ranks r0 and r1 of a device array (exact, 3 histogram passes)

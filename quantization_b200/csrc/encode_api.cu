@@ -12,8 +12,23 @@
 namespace qz {
 qz_status bin_encode_rows(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, uint32_t row_bytes,
                           uint8_t *d_out);
-qz_status dev_minmax(qz_ctx *ctx, const float *d_data, uint64_t n, uint32_t *d_mm, bool init);
-qz_status read_minmax(qz_ctx *ctx, const uint32_t *d_mm, float *mn, float *mx);
+qz_status dev_minmax(qz_ctx *ctx, const float *d_data, uint64_t n, uint32_t *d_mm, bool init, uint64_t base);
+qz_status read_minmax(qz_ctx *ctx, const uint32_t *d_mm, float *mn, float *mx, uint64_t *zero_idx);
+void fix_zero_sign(float *mn, float *mx, float first_zero);
+
+// min / max of a device-resident corpus with the reference's first-seen-zero rule
+static qz_status minmax_dev_resident(qz_ctx *ctx, const float *d_data, uint64_t n, uint32_t *d_mm, float *mn, float *mx) {
+    uint64_t zi = ~0ull;
+    QZ_TRY(dev_minmax(ctx, d_data, n, d_mm, true, 0));
+    QZ_TRY(read_minmax(ctx, d_mm, mn, mx, &zi));
+    if ((*mn == 0.0f || *mx == 0.0f) && zi != ~0ull) {
+        float z = 0.0f;
+        QZ_CUDA(ctx, cudaMemcpyAsync(&z, d_data + zi, sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        fix_zero_sign(mn, mx, z);
+    }
+    return QZ_OK;
+}
 qz_status dev_select2(qz_ctx *ctx, const float *d_vals, uint64_t n, uint64_t r0, uint64_t r1, float *v0, float *v1,
                       const uint64_t *d_ids, uint32_t dim);
 qz_status launch_u8_encode(qz_ctx *ctx, const float *d_data, uint64_t count, uint32_t dim, int distance, int invert,
@@ -144,8 +159,7 @@ qz_status qz_u8_encode_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uin
     QZ_TRY(ensure_io(ctx, 256));
     uint32_t *d_mm = reinterpret_cast<uint32_t *>(ctx->d_io);
     float mn, mx;
-    QZ_TRY(dev_minmax(ctx, d_data, count * (uint64_t)dim, d_mm, true));
-    QZ_TRY(read_minmax(ctx, d_mm, &mn, &mx));
+    QZ_TRY(minmax_dev_resident(ctx, d_data, count * (uint64_t)dim, d_mm, &mn, &mx));
     if (quantile && count >= 127 && *quantile < 1.0f) {  // quantile.rs:27-29
         const uint64_t slice = std::min<uint64_t>(count, kQuantileSample);
         bool found = false;
@@ -196,8 +210,7 @@ qz_status qz_u8_minmax_dev(qz_ctx *ctx, const float *d_data, uint64_t count, uin
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     QZ_TRY(ensure_io(ctx, 256));
     uint32_t *d_mm = reinterpret_cast<uint32_t *>(ctx->d_io);
-    QZ_TRY(dev_minmax(ctx, d_data, count * (uint64_t)dim, d_mm, true));
-    return read_minmax(ctx, d_mm, min_out, max_out);
+    return minmax_dev_resident(ctx, d_data, count * (uint64_t)dim, d_mm, min_out, max_out);
 }
 
 qz_status qz_u8_quantile_dev(qz_ctx *ctx, const float *d_sample, uint64_t n_rows, uint32_t dim, uint64_t slice_size,
@@ -270,13 +283,15 @@ qz_status qz_u8_encode(qz_ctx *ctx, const float *data, uint64_t count, uint32_t 
             e = cudaMemcpyAsync(d_chunk, data + r * dim, n * (size_t)dim * 4, cudaMemcpyHostToDevice, ctx->stream);
             if (e != cudaSuccess) st = cuda_fail(ctx, e, "qz_u8_encode: H2D");
         }
-        if (st == QZ_OK) st = dev_minmax(ctx, d_chunk, n * (uint64_t)dim, d_mm, r == 0);
+        if (st == QZ_OK) st = dev_minmax(ctx, d_chunk, n * (uint64_t)dim, d_mm, r == 0, r * (uint64_t)dim);
         if (st == QZ_OK) {
             e = cudaStreamSynchronize(ctx->stream);
             if (e != cudaSuccess) st = cuda_fail(ctx, e, "qz_u8_encode: minmax");
         }
     }
-    if (st == QZ_OK) st = read_minmax(ctx, d_mm, &mn, &mx);
+    uint64_t zero_idx = ~0ull;
+    if (st == QZ_OK) st = read_minmax(ctx, d_mm, &mn, &mx, &zero_idx);
+    if (st == QZ_OK && zero_idx != ~0ull) fix_zero_sign(&mn, &mx, data[zero_idx]);  // quantile.rs:5-19: first zero seen wins
     // pass 2: quantile cut on a sample (u8.rs:58-71)
     if (st == QZ_OK && quantile && count >= 127 && *quantile < 1.0f) {
         const uint64_t slice = std::min<uint64_t>(count, kQuantileSample);

@@ -204,6 +204,7 @@ qz_status qz_ctx_get_timing(qz_ctx *ctx, double *total_ms, uint64_t *launches) {
     return QZ_OK;
 }
 
+void *qz_ctx_stream(const qz_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 uint64_t qz_ctx_launch_count(const qz_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int32_t qz_ctx_sm_count(const qz_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
 

@@ -131,6 +131,11 @@ class Context:
         return ms.value, int(n.value)
 
     @property
+    def stream_handle(self):
+        """the cudaStream_t (as an int) the context's `*_dev` calls enqueue on"""
+        return int(self._L.qz_ctx_stream(self.handle) or 0)
+
+    @property
     def launch_count(self):
         return int(self._L.qz_ctx_launch_count(self.handle))
 

@@ -73,7 +73,7 @@ class EncodedVectorsBin(DeviceIndex):
                 os.makedirs(d, exist_ok=True)
         with open(meta_path, "w") as f:
             json.dump({"vector_parameters": self.vector_parameters.to_json()}, f, separators=(",", ":"))
-        np.ascontiguousarray(self.encoded_vectors, np.uint8).tofile(data_path)
+        self.host_storage().tofile(data_path)
 
     @classmethod
     def load(cls, data_path, meta_path, vector_parameters, *, bits_store_type=BITS_STORE_U128, ctx=None, id_base=0):
@@ -85,4 +85,8 @@ class EncodedVectorsBin(DeviceIndex):
         expected = size * vector_parameters.count
         if buf.size != expected:
             raise OSError(f"Loaded storage size {buf.size} is not equal to expected size {expected}")
-        return cls(ctx, buf, VectorParameters.from_json(meta["vector_parameters"]), bits_store_type, id_base)
+        vp = VectorParameters.from_json(meta["vector_parameters"])
+        if (vp.dim, vp.count) != (vector_parameters.dim, vector_parameters.count):
+            raise OSError(f"EncodedVectorsBin metadata describes {vp.count} x {vp.dim} vectors, the caller asked for "
+                          f"{vector_parameters.count} x {vector_parameters.dim}")
+        return cls(ctx, buf, vp, bits_store_type, id_base)

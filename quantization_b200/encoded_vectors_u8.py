@@ -119,7 +119,7 @@ class EncodedVectorsU8(DeviceIndex):
                 os.makedirs(d, exist_ok=True)
         with open(meta_path, "w") as f:
             json.dump(meta, f, separators=(",", ":"))
-        np.ascontiguousarray(self.encoded_vectors, np.uint8).tofile(data_path)
+        self.host_storage().tofile(data_path)
 
     @classmethod
     def load(cls, data_path, meta_path, vector_parameters, *, ctx=None, id_base=0):
@@ -132,4 +132,9 @@ class EncodedVectorsU8(DeviceIndex):
         if buf.size != expected:  # encoded_storage.rs:40-50
             raise OSError(f"Loaded storage size {buf.size} is not equal to expected size {expected}")
         vp = VectorParameters.from_json(meta["vector_parameters"])
+        if (vp.dim, vp.count) != (vector_parameters.dim, vector_parameters.count):
+            # the storage was size-checked against the CALLER's parameters; an index built from metadata that
+            # disagrees with them would read past the loaded bytes (a stale or foreign meta file)
+            raise OSError(f"EncodedVectorsU8 metadata describes {vp.count} x {vp.dim} vectors, the caller asked for "
+                          f"{vector_parameters.count} x {vector_parameters.dim}")
         return cls(ctx, buf, vp, meta["alpha"], meta["offset"], meta["multiplier"], id_base)

@@ -114,6 +114,27 @@ class ShardedSearch:
             self.index.ctx._L.qz_peer_destroy(self._peer)
             self._peer = None
 
+    def _order(self, ctx_first):
+        """Make work on one of (the qz Context's stream, torch's current stream) wait for what has been enqueued on
+        the other.  A no-op when they are the same stream (bench.py creates the Context on torch's stream) and on
+        the CPU test path; with the default Context (its own non-blocking stream) the all-gather could otherwise
+        read the keys before the scan has written them."""
+        if self.index is None or self.device.type != "cuda":
+            return
+        t = self.torch
+        cur = t.cuda.current_stream(self.device)
+        cs = self.index.ctx.stream_handle
+        if cs == cur.cuda_stream:
+            return
+        ext = t.cuda.ExternalStream(cs, device=self.device)
+        ev = t.cuda.Event()
+        if ctx_first:
+            ev.record(ext)
+            cur.wait_event(ev)
+        else:
+            ev.record(cur)
+            ext.wait_event(ev)
+
     # ---- the step ------------------------------------------------------------------------------------
     def search_top_k_dev(self, d_query, k, largest=True):
         """asynchronous on the current stream; returns device tensors (scores[k], ids[k]) valid on every rank"""
@@ -125,11 +146,14 @@ class ShardedSearch:
                                                    C.c_void_p(d_ids.data_ptr())))
             return d_scores, d_ids
         self._local_topk(d_query, k, largest, d_keys)
+        self._order(ctx_first=True)   # the collective (torch's stream) reads what the scan (context stream) wrote
         if self.world > 1:
             self.dist.all_gather_into_tensor(d_all, d_keys, group=self.group)
         else:
             d_all.copy_(d_keys)
+        self._order(ctx_first=False)  # the merge (context stream) reads what the collective wrote
         self._merge(d_all, self.world, k, largest, d_scores, d_ids)
+        self._order(ctx_first=True)   # the caller reads the results on torch's stream
         return d_scores, d_ids
 
     def search(self, query_f32, k, largest=True):
@@ -270,12 +294,24 @@ class ShardedEncodeU8:
         lo, hi = shard_range(vp.count, self.rank, self.world)
         assert tuple(d_rows.shape) == (hi - lo, vp.dim), "rank holds rows shard_range(count, rank, world)"
         mn, mx = self._minmax(d_rows)
-        if self.world > 1:  # min / max are exact under any grouping: the sharded fold equals quantile.rs:5-19
-            d_mn = t.tensor([mn], dtype=t.float32, device=self.device)
-            d_mx = t.tensor([mx], dtype=t.float32, device=self.device)
-            dist.all_reduce(d_mn, op=dist.ReduceOp.MIN, group=self.group)
-            dist.all_reduce(d_mx, op=dist.ReduceOp.MAX, group=self.group)
-            mn, mx = float(d_mn.item()), float(d_mx.item())
+        if self.world > 1:
+            # The reference folds with strict < and > in id order (quantile.rs:5-19): of equal extremes — i.e. zeros
+            # of different sign — it keeps the first.  Ranks hold ascending id ranges, so the per-rank (min, max)
+            # pairs are gathered and folded in rank order with the same strict comparisons (a MIN / MAX all-reduce
+            # would leave the sign of a zero to the collective's implementation).
+            d_mine = t.tensor([mn, mx], dtype=t.float32, device=self.device)
+            d_all = t.zeros(2 * self.world, dtype=t.float32, device=self.device)
+            dist.all_gather_into_tensor(d_all, d_mine, group=self.group)
+            pairs = d_all.cpu().numpy().reshape(self.world, 2)
+            mn, mx = np.float32(np.finfo(np.float32).max), np.float32(np.finfo(np.float32).min)
+            for r in range(self.world):
+                if shard_range(vp.count, r, self.world)[0] == shard_range(vp.count, r, self.world)[1]:
+                    continue  # an empty shard contributes the fold's identity
+                if pairs[r, 0] < mn:
+                    mn = pairs[r, 0]
+                if pairs[r, 1] > mx:
+                    mx = pairs[r, 1]
+            mn, mx = float(mn), float(mx)
         if quantile is not None and vp.count >= 127 and quantile < 1.0:  # quantile.rs:27-29
             slice_size = min(vp.count, QUANTILE_SAMPLE)
             ids = sample_ids(vp.count, slice_size, seed) if ids is None else np.sort(np.asarray(ids, np.uint64))

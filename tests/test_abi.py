@@ -36,6 +36,26 @@ def test_pure_host_entry_points():
     assert [L.qz_bin_row_bytes(d, 16) for d in (1, 387, 1536)] == [16, 64, 192]
 
 
+def test_header_compiles_as_c99_and_links(tmp_path):
+    """include/qz_cuda.h is a plain C header: tests/abi_smoke.c (C99, -pedantic -Werror) includes it, takes the address
+    of every declared function, links -lqz_cuda and runs (the boundary a cgo / bindgen / C host sees)"""
+    import subprocess
+    from quantization_b200 import _lib, build
+    build.build()
+    src = os.path.join(ROOT, "tests", "abi_smoke.c")
+    text = open(src).read()
+    for sym in header_symbols():
+        assert f"F({sym})" in text, f"{sym} is declared in qz_cuda.h but not referenced by tests/abi_smoke.c"
+    exe = str(tmp_path / "abi_smoke")
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", src, "-I", os.path.join(ROOT, "include"),
+                        "-L", libdir, "-lqz_cuda", f"-Wl,-rpath,{libdir}", "-Wl,-rpath,/usr/local/cuda/lib64", "-o", exe],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "abi_smoke:" in r.stdout, r.stdout + r.stderr
+
+
 def test_no_gpu_fails_loudly():
     """Without a device the context constructor must raise, never fall back."""
     import pytest

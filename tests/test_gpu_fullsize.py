@@ -171,3 +171,58 @@ def test_c1_u8_100k_host_path(ctx, dim):
     ia, ib = rng.integers(0, count, 2000).astype(np.uint32), rng.integers(0, count, 2000).astype(np.uint32)
     assert np.array_equal(bits(g.score_pairs(ia, ib)), bits(o.score_pairs(ia, ib)))
     assert bits(np.float32(g.score_point(enc, 123)))[()] == bits(np.float32(o.score_point(o.encode_query(query), 123)))[()]
+
+
+def test_c5_batch_1p25m_x_768(ctx):
+    """BASELINE config 5 at one GPU's share of its configured size: 4096 queries x 1.25M rows x 768-d through
+    qz_u8_search_batch_dev (tcgen05 int8 contraction).  This is the size at which the batched path walks its whole
+    chunk schedule (bootstrap chunks, growing chunks, threshold refresh between them).  Every query's top-100 must be
+    bit-identical to the single-query scan (row_scan_kernel, itself pinned against the reference scorers in
+    test_c2_*), and 32 of them are compared with the oracle directly — encode_query (u8.rs:290-329), the reference's
+    AVX2 dot kernel (cpp/avx2.c:31-69), the score map of u8.rs:347 and the caller-side heap — on all 1.25M rows."""
+    count, dim, nq = 1_250_000, 768, 4096
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev); g.manual_seed(42)
+    data = torch.rand((count, dim), generator=g, device=dev)
+    queries = torch.rand((nq, dim), generator=g, device=dev)
+    torch.cuda.synchronize()  # the context has its own stream
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
+    ix = qz.EncodedVectorsU8.encode_dev(data.data_ptr(), vp, None, ctx=ctx)
+    del data
+    d_s = torch.zeros((nq, K), dtype=torch.float32, device=dev)
+    d_i = torch.zeros((nq, K), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    for rep in range(2):  # the second call reuses the device-side mirror and scratch of the first
+        ix.search_batch_dev(queries.data_ptr(), nq, K, True, d_s.data_ptr(), d_i.data_ptr())
+    ctx.synchronize()
+    bs, bi = d_s.cpu().numpy(), d_i.cpu().numpy().view(np.uint32)
+    # every query against the single-query scan on the device
+    d_enc = torch.zeros((nq, dim + 4), dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+    ix.encode_query_dev(queries.data_ptr(), nq, d_enc.data_ptr())
+    d_ss = torch.zeros((nq, K), dtype=torch.float32, device=dev)
+    d_si = torch.zeros((nq, K), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()  # (torch's zero fills run on its own stream)
+    for qi in range(nq):
+        ix.search_top_k_dev(d_enc[qi].data_ptr(), K, True, 0, d_ss[qi].data_ptr(), d_si[qi].data_ptr())
+    ctx.synchronize()
+    ss, si = d_ss.cpu().numpy(), d_si.cpu().numpy().view(np.uint32)
+    bad = np.nonzero((bi != si).any(axis=1) | (bits(bs) != bits(ss)).any(axis=1))[0]
+    assert bad.size == 0, f"batched top-100 differs from the single-query scan for queries {bad[:10]}"
+    # 32 queries against the oracle (the reference's own AVX2 scorer over all rows)
+    storage = ix.download()
+    o = O.OracleU8(storage, count, dim, 0, False, ix.alpha, ix.offset, ix.multiplier)
+    qh = queries.cpu().numpy()
+    for qi in range(0, nq, nq // 32):
+        enc = o.encode_query(qh[qi])
+        os_, oi = o.search(enc, K, True, threads=THREADS)
+        assert np.array_equal(bi[qi], oi), f"query {qi}: batched ids differ from the reference scorers"
+        assert np.array_equal(bits(bs[qi]), bits(os_)), f"query {qi}: batched scores differ"
+    # smallest-first over the same corpus (the other filter direction), 128 queries
+    ix.search_batch_dev(queries.data_ptr(), 128, K, False, d_s.data_ptr(), d_i.data_ptr())
+    ctx.synchronize()
+    bs, bi = d_s[:128].cpu().numpy(), d_i[:128].cpu().numpy().view(np.uint32)
+    for qi in (0, 77, 127):
+        os_, oi = o.search(o.encode_query(qh[qi]), K, False, threads=THREADS)
+        assert np.array_equal(bi[qi], oi) and np.array_equal(bits(bs[qi]), bits(os_))
+    ix.close()
