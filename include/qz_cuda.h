@@ -297,6 +297,16 @@ QZ_API qz_status qz_scan_topk_peer_dev(qz_index *index, qz_peer *peer, const voi
  * one synchronisation; *n_out = min(k, rows over all shards) */
 QZ_API qz_status qz_search_topk_peer(qz_index *index, qz_peer *peer, const float *query, uint32_t k, int32_t largest,
                                      float *scores, uint32_t *ids, uint32_t *n_out);
+/* Rooted form — the gather BASELINE.json's north_star names: only rank `root` waits for the other ranks' keys and
+ * merges; its outputs hold the global top-k.  Every other rank stores its k keys into the root's buffer, raises its
+ * flag and finishes its launch without waiting for anybody (it may run up to two steps ahead of the root; the root's
+ * acknowledgement, written back over NVLink after each merge, is the flow control) — its outputs are NOT written
+ * and the host form returns *n_out = 0 without synchronising.  Same call sequence on every rank, like a collective;
+ * rooted and all-to-all steps may be mixed on one peer group. */
+QZ_API qz_status qz_scan_topk_gather_dev(qz_index *index, qz_peer *peer, uint32_t root, const void *d_enc_query,
+                                         uint32_t k, int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
+QZ_API qz_status qz_search_topk_gather(qz_index *index, qz_peer *peer, uint32_t root, const float *query, uint32_t k,
+                                       int32_t largest, float *scores, uint32_t *ids, uint32_t *n_out);
 
 #ifdef __cplusplus
 }

@@ -83,6 +83,8 @@ _SIGS = {
     "qz_peer_destroy": (None, [vp]),
     "qz_scan_topk_peer_dev": (C.c_int32, [vp, vp, vp, C.c_uint32, C.c_int32, vp, vp, vp]),
     "qz_search_topk_peer": (C.c_int32, [vp, vp, vp, C.c_uint32, C.c_int32, vp, vp, u32p]),
+    "qz_scan_topk_gather_dev": (C.c_int32, [vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int32, vp, vp, vp]),
+    "qz_search_topk_gather": (C.c_int32, [vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int32, vp, vp, u32p]),
 }
 
 _lib = None

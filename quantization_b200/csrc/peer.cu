@@ -13,6 +13,10 @@
 struct qz_peer {
     qz_ctx *ctx = nullptr;
     uint32_t world = 0, rank = 0, seq = 0;
+    uint32_t last_read[2][qz::kMaxPeers] = {};  // per buffer half and rank: the last step in which that rank read the half
+    cudaEvent_t staged = nullptr;     // rooted host form on a non-root rank: the query's H2D copy out of the pinned
+    bool staged_pending = false;      // staging buffer (the call returns without synchronising; the next one must
+                                      // not overwrite the staging buffer before that copy has run)
     uint8_t *local = nullptr;            // gather[2][world][kPeerStride] u64, then flags[2][world] u32
     uint8_t *mapped[qz::kMaxPeers] = {};  // peers' buffers in this process (mapped[rank] = local)
     bool connected = false;
@@ -86,12 +90,13 @@ void qz_peer_destroy(qz_peer *pe) {
     for (uint32_t r = 0; r < pe->world; r++)
         if (r != pe->rank && pe->mapped[r]) cudaIpcCloseMemHandle(pe->mapped[r]);
     cudaFree(pe->local);
+    if (pe->staged) cudaEventDestroy(pe->staged);
     delete pe;
     ctx_release(ctx);
 }
 
-qz_status qz_scan_topk_peer_dev(qz_index *ix, qz_peer *pe, const void *d_enc_query, uint32_t k, int32_t largest,
-                                uint64_t *d_keys, float *d_scores, uint32_t *d_ids) {
+static qz_status scan_topk_exchange(qz_index *ix, qz_peer *pe, int32_t root, const void *d_enc_query, uint32_t k,
+                                    int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids) {
     if (!ix || !ix->ctx || !pe) return QZ_ARGUMENTS;
     qz_ctx *ctx = ix->ctx;
     if (pe->ctx != ctx) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: index and peer group live on different contexts");
@@ -99,6 +104,7 @@ qz_status qz_scan_topk_peer_dev(qz_index *ix, qz_peer *pe, const void *d_enc_que
     if (k == 0 || k > kPeerStride) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: k must be in [1, 128]");
     if (ix->count == 0) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: empty shard");
     if (!d_enc_query) return fail(ctx, QZ_ARGUMENTS, "scan_topk_peer: NULL query");
+    if (root >= (int32_t)pe->world) return fail(ctx, QZ_ARGUMENTS, "scan_topk_gather: root must be a rank of the group");
     if (pe->world == 1) return qz_scan_topk_dev(ix, d_enc_query, k, largest, d_keys, d_scores, d_ids);
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     PeerExchange x{};
@@ -106,7 +112,9 @@ qz_status qz_scan_topk_peer_dev(qz_index *ix, qz_peer *pe, const void *d_enc_que
     x.rank = pe->rank;
     x.seq = ++pe->seq;
     x.buf = x.seq & 1;
+    x.root = root;
     for (uint32_t r = 0; r < pe->world; r++) {
+        x.need_ack[r] = pe->last_read[x.buf][r];  // (see PeerExchange: flow control)
         x.gather[r] = reinterpret_cast<uint64_t *>(pe->mapped[r]);
         x.flags[r] = reinterpret_cast<uint32_t *>(pe->mapped[r] + gather_bytes(pe->world));
     }
@@ -134,14 +142,30 @@ qz_status qz_scan_topk_peer_dev(qz_index *ix, qz_peer *pe, const void *d_enc_que
     } else {
         st = launch_row_scan(ix, d_enc_query, nullptr, k, largest, &n_lists, &Kp, &fin);
     }
-    if (st != QZ_OK) pe->seq--;  // the exchange did not happen
+    if (st != QZ_OK) {
+        pe->seq--;  // the exchange did not happen
+        return st;
+    }
+    for (uint32_t r = 0; r < pe->world; r++)
+        if (root < 0 || (uint32_t)root == r) pe->last_read[x.buf][r] = x.seq;
     return st;
 }
 
+qz_status qz_scan_topk_peer_dev(qz_index *ix, qz_peer *pe, const void *d_enc_query, uint32_t k, int32_t largest,
+                                uint64_t *d_keys, float *d_scores, uint32_t *d_ids) {
+    return scan_topk_exchange(ix, pe, -1, d_enc_query, k, largest, d_keys, d_scores, d_ids);
+}
+
+qz_status qz_scan_topk_gather_dev(qz_index *ix, qz_peer *pe, uint32_t root, const void *d_enc_query, uint32_t k,
+                                  int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids) {
+    return scan_topk_exchange(ix, pe, (int32_t)root, d_enc_query, k, largest, d_keys, d_scores, d_ids);
+}
+
 // encode_query + scan + cross-GPU exchange, host buffers, one synchronisation (the multi-GPU form of qz_search_topk).
-// *n_out = number of results = min(k, sum of the shards' rows) — unfilled slots are dropped.
-qz_status qz_search_topk_peer(qz_index *ix, qz_peer *pe, const float *query, uint32_t k, int32_t largest, float *scores,
-                              uint32_t *ids, uint32_t *n_out) {
+// *n_out = number of results = min(k, sum of the shards' rows) — unfilled slots are dropped; rooted form: 0 on a
+// rank that is not the root (its outputs are not written and it does not wait for anyone).
+static qz_status search_topk_exchange(qz_index *ix, qz_peer *pe, int32_t root, const float *query, uint32_t k,
+                                      int32_t largest, float *scores, uint32_t *ids, uint32_t *n_out) {
     if (!ix || !ix->ctx || !pe) return QZ_ARGUMENTS;
     qz_ctx *ctx = ix->ctx;
     if (!scores || !ids || !query) return fail(ctx, QZ_ARGUMENTS, "search_topk_peer: NULL argument");
@@ -154,13 +178,28 @@ qz_status qz_search_topk_peer(qz_index *ix, qz_peer *pe, const float *query, uin
     QZ_TRY(ensure_query(ctx, fb_pad + qb_pad + 16));
     QZ_TRY(ensure_pin(ctx, fb_pad + (size_t)2 * QZ_MAX_K * 4));
     uint8_t *d_f32 = ctx->d_query, *d_blob = ctx->d_query + fb_pad;
+    if (pe->staged_pending) {
+        QZ_CUDA(ctx, cudaEventSynchronize(pe->staged));
+        pe->staged_pending = false;
+    }
     memcpy(ctx->h_pin, query, fb);
     QZ_CUDA(ctx, cudaMemcpyAsync(d_f32, ctx->h_pin, fb, cudaMemcpyHostToDevice, ctx->stream));
+    if (root >= 0 && pe->world > 1 && (uint32_t)root != pe->rank) {
+        if (!pe->staged) QZ_CUDA(ctx, cudaEventCreateWithFlags(&pe->staged, cudaEventDisableTiming));
+        QZ_CUDA(ctx, cudaEventRecord(pe->staged, ctx->stream));
+        pe->staged_pending = true;
+    }
     QZ_TRY(qz_encode_query_dev(ix, reinterpret_cast<const float *>(d_f32), 1, d_blob));
-    QZ_TRY(qz_scan_topk_peer_dev(ix, pe, d_blob, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
+    // the k ids go right behind the k scores: one copy of 2 * k * 4 bytes brings both back
+    QZ_TRY(scan_topk_exchange(ix, pe, root, d_blob, k, largest, nullptr, ctx->d_scores_k,
+                              reinterpret_cast<uint32_t *>(ctx->d_scores_k + k)));
+    if (root >= 0 && pe->world > 1 && (uint32_t)root != pe->rank) {  // not the root: nothing comes back
+        if (n_out) *n_out = 0;
+        return QZ_OK;  // (asynchronous: the launch is on the stream; the caller's next call or qz_ctx_synchronize orders it)
+    }
     float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
-    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + QZ_MAX_K);
-    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, ((size_t)QZ_MAX_K + k) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + k);
+    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)2 * k * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     uint32_t m = 0;
     while (m < k && hi[m] != 0xFFFFFFFFu) m++;  // empty slots decode to id 0xFFFFFFFF
@@ -168,6 +207,16 @@ qz_status qz_search_topk_peer(qz_index *ix, qz_peer *pe, const float *query, uin
     memcpy(ids, hi, (size_t)m * 4);
     if (n_out) *n_out = m;
     return QZ_OK;
+}
+
+qz_status qz_search_topk_peer(qz_index *ix, qz_peer *pe, const float *query, uint32_t k, int32_t largest, float *scores,
+                              uint32_t *ids, uint32_t *n_out) {
+    return search_topk_exchange(ix, pe, -1, query, k, largest, scores, ids, n_out);
+}
+
+qz_status qz_search_topk_gather(qz_index *ix, qz_peer *pe, uint32_t root, const float *query, uint32_t k, int32_t largest,
+                                float *scores, uint32_t *ids, uint32_t *n_out) {
+    return search_topk_exchange(ix, pe, (int32_t)root, query, k, largest, scores, ids, n_out);
 }
 
 }  // extern "C"

@@ -207,10 +207,12 @@ qz_status qz_scan_topk(qz_index *ix, const void *enc_query, uint32_t k, int32_t 
         memcpy(ctx->h_pin, enc_query, qb);
         QZ_CUDA(ctx, cudaMemcpyAsync(ctx->d_query, ctx->h_pin, qb, cudaMemcpyHostToDevice, ctx->stream));
     }
-    QZ_TRY(qz_scan_topk_dev(ix, ctx->d_query, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
+    // the k ids go right behind the k scores: one copy of 2 * k * 4 bytes brings both back
+    QZ_TRY(qz_scan_topk_dev(ix, ctx->d_query, k, largest, nullptr, ctx->d_scores_k,
+                            reinterpret_cast<uint32_t *>(ctx->d_scores_k + k)));
     float *hs = reinterpret_cast<float *>(ctx->h_pin + qb_pad);
-    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + QZ_MAX_K);
-    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, ((size_t)QZ_MAX_K + k) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + k);
+    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)2 * k * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const uint32_t m = (uint32_t)(ix->count < k ? ix->count : k);
     memcpy(scores, hs, (size_t)m * 4);
@@ -238,10 +240,11 @@ qz_status qz_search_topk(qz_index *ix, const float *query, uint32_t k, int32_t l
         QZ_CUDA(ctx, cudaMemcpyAsync(d_f32, ctx->h_pin, fb, cudaMemcpyHostToDevice, ctx->stream));
         QZ_TRY(qz_encode_query_dev(ix, reinterpret_cast<const float *>(d_f32), 1, d_blob));
     }
-    QZ_TRY(qz_scan_topk_dev(ix, d_blob, k, largest, nullptr, ctx->d_scores_k, ctx->d_ids_k));
+    QZ_TRY(qz_scan_topk_dev(ix, d_blob, k, largest, nullptr, ctx->d_scores_k,
+                            reinterpret_cast<uint32_t *>(ctx->d_scores_k + k)));
     float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
-    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + QZ_MAX_K);
-    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, ((size_t)QZ_MAX_K + k) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + k);
+    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)2 * k * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const uint32_t m = (uint32_t)(ix->count < k ? ix->count : k);
     memcpy(scores, hs, (size_t)m * 4);

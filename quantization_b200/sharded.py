@@ -55,9 +55,11 @@ def results_to_keys(scores, ids, largest):
 class ShardedSearch:
     """search_top_k over all ranks' shards; every rank returns the same (scores, ids)."""
 
-    def __init__(self, index=None, group=None, device=None, *, local_topk=None, merge=None, peer=False):
+    def __init__(self, index=None, group=None, device=None, *, local_topk=None, merge=None, peer=False, root=None):
         """peer=True: exchange through peer memory inside the scan launch (qz_scan_topk_peer_dev: one kernel per
-        query per GPU, no collective call) instead of all-gather + merge.  k <= 128."""
+        query per GPU, no collective call) instead of all-gather + merge.  k <= 128.
+        root=r (with peer=True): the rooted gather (qz_scan_topk_gather_dev) — only rank r ends with the global top-k,
+        the other ranks publish their keys and never wait."""
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -70,6 +72,7 @@ class ShardedSearch:
         self._merge = merge if merge is not None else self._gpu_merge
         self._bufs = {}
         self._peer = None
+        self.root = root
         if peer and self.world > 1:
             self._peer_setup()
 
@@ -141,6 +144,11 @@ class ShardedSearch:
         d_keys, d_all, d_scores, d_ids = self._buffers(k)
         if self._peer is not None:
             ctx = self.index.ctx
+            if self.root is not None:
+                ctx.check(ctx._L.qz_scan_topk_gather_dev(self.index.handle, self._peer, self.root, C.c_void_p(d_query), k,
+                                                         int(bool(largest)), None, C.c_void_p(d_scores.data_ptr()),
+                                                         C.c_void_p(d_ids.data_ptr())))
+                return d_scores, d_ids  # (the global result on rank `root` only)
             ctx.check(ctx._L.qz_scan_topk_peer_dev(self.index.handle, self._peer, C.c_void_p(d_query), k,
                                                    int(bool(largest)), None, C.c_void_p(d_scores.data_ptr()),
                                                    C.c_void_p(d_ids.data_ptr())))
@@ -164,6 +172,11 @@ class ShardedSearch:
         ctx = self.index.ctx
         q = np.ascontiguousarray(query_f32, np.float32).reshape(-1)
         scores, ids, n = np.empty(k, np.float32), np.empty(k, np.uint32), C.c_uint32(0)
+        if self.root is not None:
+            ctx.check(ctx._L.qz_search_topk_gather(self.index.handle, self._peer, self.root, C.c_void_p(q.ctypes.data), k,
+                                                   int(bool(largest)), C.c_void_p(scores.ctypes.data),
+                                                   C.c_void_p(ids.ctypes.data), C.byref(n)))
+            return scores[: n.value], ids[: n.value]  # empty on the ranks that are not the root
         ctx.check(ctx._L.qz_search_topk_peer(self.index.handle, self._peer, C.c_void_p(q.ctypes.data), k,
                                              int(bool(largest)), C.c_void_p(scores.ctypes.data),
                                              C.c_void_p(ids.ctypes.data), C.byref(n)))

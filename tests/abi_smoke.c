@@ -26,7 +26,7 @@ static const struct {
     F(qz_scan_topk_dev), F(qz_search_topk), F(qz_scan_scores), F(qz_scan_scores_dev), F(qz_score_points), F(qz_score_pairs),
     F(qz_score_points_dev), F(qz_score_pairs_dev), F(qz_merge_topk_dev), F(qz_host_pin), F(qz_host_unpin),
     F(qz_scan_topk_chunked), F(qz_peer_create), F(qz_peer_connect), F(qz_peer_destroy), F(qz_scan_topk_peer_dev),
-    F(qz_search_topk_peer),
+    F(qz_search_topk_peer), F(qz_scan_topk_gather_dev), F(qz_search_topk_gather),
 };
 
 int main(void) {

@@ -1,8 +1,10 @@
 """Multi-GPU check of the peer-memory top-k exchange (run under torchrun, one rank per GPU).
 
 Every rank encodes the same seeded corpus, keeps its own point-id range, and answers the same queries three ways:
-the peer-memory exchange fused into the scan launch (qz_scan_topk_peer_dev), the all-gather + merge path, and a
-single-GPU scan of the whole corpus on rank 0's device memory budget permitting.  All three must agree bit for bit.
+the peer-memory exchange fused into the scan launch (qz_scan_topk_peer_dev), its rooted form (qz_scan_topk_gather_dev:
+only the root waits and merges; rooted and all-to-all steps are interleaved on ONE peer group, and the non-root
+ranks are allowed to run ahead), the all-gather + merge path, and a single-GPU scan of the whole corpus.  All must
+agree bit for bit (the rooted form on its root).
 Prints per-step device times of both exchange paths.
 """
 import os
@@ -57,19 +59,43 @@ def main():
             q = np.random.default_rng(100 + qi).random(dim, dtype=np.float32) - (0.5 if codec == "bin" else 0.0)
             enc = full.encode_query(q)
             d_q = torch.from_numpy(np.frombuffer(bytes(enc), np.uint8).copy()).to(dev)
-            for k, largest in ((100, True), (1, True), (128, False), (17, True)):
+            for k, largest in [tuple(map(int, t.split(":"))) for t in os.environ.get("PEER_CHECK_KS", "100:1,1:1,128:0,17:1").split(",")]:
                 a_s, a_i = s_peer.search_top_k(d_q.data_ptr(), k, largest, count)
                 b_s, b_i = s_nccl.search_top_k(d_q.data_ptr(), k, largest, count)
                 r_s, r_i = full.search_top_k(enc, k, largest)
                 same = (np.array_equal(a_i, b_i) and np.array_equal(a_i, r_i)
                         and np.array_equal(a_s.view(np.uint32), r_s.view(np.uint32))
                         and np.array_equal(b_s.view(np.uint32), r_s.view(np.uint32)))
+                # rooted gather on the same peer group, several steps back to back without a host synchronisation
+                # in between (non-root ranks run ahead; the root's acknowledgement is the only flow control), with
+                # a changing root and an all-to-all step in the middle
+                for root in ((world - 1, 0) if os.environ.get("PEER_CHECK_REV") else (0, world - 1)):
+                    if os.environ.get("PEER_CHECK_TRACE"):
+                        torch.cuda.synchronize()
+                        print(f"[trace] rank {rank} {codec} {count} q{qi} k={k} root={root}", file=sys.stderr, flush=True)
+                    s_peer.root = root
+                    for _ in range(5):
+                        g_s, g_i = s_peer.search_top_k_dev(d_q.data_ptr(), k, largest)
+                        if os.environ.get("PEER_CHECK_TRACE"):
+                            torch.cuda.synchronize()
+                            print(f"[trace] rank {rank} rooted step done", file=sys.stderr, flush=True)
+                    s_peer.root = None
+                    s_peer.search_top_k_dev(d_q.data_ptr(), k, largest)
+                    s_peer.root = root
+                    g_s, g_i = s_peer.search_top_k_dev(d_q.data_ptr(), k, largest)
+                    torch.cuda.synchronize()
+                    if rank == root:
+                        n = min(k, count)
+                        gs, gi = g_s.cpu().numpy()[:n], g_i.cpu().numpy().view(np.uint32)[:n]
+                        same = same and np.array_equal(gi, r_i) and np.array_equal(gs.view(np.uint32), r_s.view(np.uint32))
+                s_peer.root = None
                 if not same:
                     ok = False
                     print(f"rank {rank}: MISMATCH {codec} {count}x{dim} q{qi} k={k} largest={largest}", flush=True)
         # timing: device time per step, max over ranks
         if count >= 100_000:
-            for name, s in (("peer", s_peer), ("nccl", s_nccl)):
+            for name, s in (("peer", s_peer), ("gather", s_peer), ("nccl", s_nccl)):
+                s_peer.root = 0 if name == "gather" else None
                 for _ in range(20):
                     s.search_top_k_dev(d_q.data_ptr(), 100, True)
                 dist.barrier()
@@ -84,6 +110,7 @@ def main():
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 if rank == 0:
                     print(f"{codec} {count}x{dim} world {world} {name}: {t.item() * 1000:.1f} us/step", flush=True)
+            s_peer.root = None
         s_peer.close()
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
