@@ -264,6 +264,18 @@ QZ_API qz_status qz_score_pairs_dev(qz_index *index, const uint32_t *d_rows_a, c
 QZ_API qz_status qz_merge_topk_dev(qz_ctx *ctx, const uint64_t *d_keys_in, uint32_t n_lists, uint32_t k,
                                    int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
 
+/* qz_merge_topk_dev without any allocation behind it.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same results bit for bit; the intermediate lists of the multi-level
+ * merge live in a 2 MiB file-scope __device__ array of the library (csrc/no_alloc.cu; held by every GPU that loads
+ * the library until the process exits) instead of the context's cudaMalloc'ed scratch, and the call itself makes no
+ * cudaMalloc / cudaFree / allocating library call.  n_lists > QZ_MERGE_STATIC_MAX_LISTS is refused with
+ * QZ_ARGUMENTS (text in qz_last_error).  Every call on a device shares the array: calls on one stream are ordered
+ * and safe, calls that overlap on the GPU (two streams or two contexts on one device) race on it. */
+#define QZ_MERGE_STATIC_MAX_LISTS 4096
+QZ_API qz_status qz_merge_topk_static_dev(qz_ctx *ctx, const uint64_t *d_keys_in, uint32_t n_lists, uint32_t k,
+                                          int32_t largest, uint64_t *d_keys, float *d_scores, uint32_t *d_ids);
+
 /* ---- out-of-core scan ---------------------------------------------------------------------------
  * The encoded storage stays in host memory (any EncodedStorage backend that can hand out contiguous runs of rows,
  * encoded_storage.rs:7-25; corpora larger than HBM) and is streamed through two device buffers: `buf_a` / `buf_b`

@@ -75,6 +75,7 @@ _SIGS = {
     "qz_score_points_dev": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
     "qz_score_pairs_dev": (C.c_int32, [vp, vp, vp, C.c_uint64, vp]),
     "qz_merge_topk_dev": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp, vp]),
+    "qz_merge_topk_static_dev": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.c_int32, vp, vp, vp]),
     "qz_host_pin": (C.c_int32, [vp, vp, C.c_uint64]),
     "qz_host_unpin": (C.c_int32, [vp, vp]),
     "qz_scan_topk_chunked": (C.c_int32, [vp, vp, vp, C.c_uint64, vp, C.c_uint32, C.c_int32, vp, vp, u32p]),

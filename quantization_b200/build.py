@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libqz_cuda.so")
-SOURCES = ["qz_ctx.cu", "qz_api.cu", "row_scan.cu", "row_scan_dot.cu", "row_scan_l1.cu", "row_scan_xor.cu", "point_kernels.cu", "pq.cu", "pq_scan2.cu", "encode.cu", "encode_api.cu", "kmeans.cu", "pq_encode_api.cu", "u8_batch.cu", "peer.cu", "chunked.cu"]
+SOURCES = ["qz_ctx.cu", "qz_api.cu", "row_scan.cu", "row_scan_dot.cu", "row_scan_l1.cu", "row_scan_xor.cu", "point_kernels.cu", "pq.cu", "pq_scan2.cu", "encode.cu", "encode_api.cu", "kmeans.cu", "pq_encode_api.cu", "u8_batch.cu", "peer.cu", "chunked.cu", "no_alloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",

@@ -24,7 +24,7 @@ static const struct {
     F(qz_index_destroy), F(qz_index_codec), F(qz_index_count), F(qz_index_row_bytes), F(qz_query_bytes),
     F(qz_index_storage_dev), F(qz_index_download), F(qz_encode_query), F(qz_encode_query_dev), F(qz_scan_topk),
     F(qz_scan_topk_dev), F(qz_search_topk), F(qz_scan_scores), F(qz_scan_scores_dev), F(qz_score_points), F(qz_score_pairs),
-    F(qz_score_points_dev), F(qz_score_pairs_dev), F(qz_merge_topk_dev), F(qz_host_pin), F(qz_host_unpin),
+    F(qz_score_points_dev), F(qz_score_pairs_dev), F(qz_merge_topk_dev), F(qz_merge_topk_static_dev), F(qz_host_pin), F(qz_host_unpin),
     F(qz_scan_topk_chunked), F(qz_peer_create), F(qz_peer_connect), F(qz_peer_destroy), F(qz_scan_topk_peer_dev),
     F(qz_search_topk_peer), F(qz_scan_topk_gather_dev), F(qz_search_topk_gather),
 };
