@@ -47,7 +47,9 @@ __global__ void __launch_bounds__(256) pq_lut_kernel(const float *queries, uint3
     lut[(size_t)ch * kPqCentroids + c] = invert ? -s : s;
 }
 
-// perm[slice][(b*256 + c)*32 + w] = lut[(slice*128 + 4*w + b)*256 + c]   (0 beyond n_chunks)
+// perm[slice][(b >> 1)*16384 + c*64 + (b & 1)*32 + w] = lut[(slice*128 + 4*w + b)*256 + c]   (0 beyond n_chunks):
+// lane w's four gathers (b = 0..3) fall in bank w whatever the codes, and a code's byte offset (c * 256) leaves the
+// low byte free for the lane's own offset, so one byte permute forms the whole variable part of the address
 __global__ void __launch_bounds__(256) pq_lut_permute_kernel(const float *lut, uint32_t n_chunks, float *perm) {
     const uint32_t slice = blockIdx.y;
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < (uint32_t)kSliceFloats;
@@ -57,7 +59,7 @@ __global__ void __launch_bounds__(256) pq_lut_permute_kernel(const float *lut, u
         const uint32_t ch = slice * kSliceChunks + cl;
         const float v = ch < n_chunks ? lut[(size_t)ch * kPqCentroids + c] : 0.0f;
         const uint32_t w = cl >> 2, b = cl & 3;
-        perm[(size_t)slice * kSliceFloats + (b * kPqCentroids + c) * 32 + w] = v;
+        perm[(size_t)slice * kSliceFloats + (b >> 1) * 16384 + c * 64 + (b & 1) * 32 + w] = v;
     }
 }
 
@@ -72,7 +74,7 @@ struct PqScanParams {
 
 // grid = (row CTAs, slices).  Each CTA keeps its 128 KiB LUT slice in shared memory; a warp scores
 // 16 rows per step: lane w owns code word w of the slice (4 chunks), so its four gathers
-// ((b*256+code)*32 + w) always fall in bank w: conflict free for any codes.
+// (layout of pq_lut_permute_kernel) always fall in bank w: conflict free for any codes.
 __global__ void __launch_bounds__(kPqWarps * 32, 1) pq_scan_kernel(PqScanParams p) {
     extern __shared__ __align__(128) float slut[];
     __shared__ __align__(8) uint64_t bar;
@@ -118,10 +120,10 @@ __global__ void __launch_bounds__(kPqWarps * 32, 1) pq_scan_kernel(PqScanParams 
 #pragma unroll
         for (int r = 0; r < 16; r++) {
             // chunks past n_chunks gather the zero padding of the permuted LUT
-            float s = my[((cw[r] & 0xFFu)) * 32];
-            s = __fadd_rn(s, my[(256 + ((cw[r] >> 8) & 0xFFu)) * 32]);
-            s = __fadd_rn(s, my[(512 + ((cw[r] >> 16) & 0xFFu)) * 32]);
-            s = __fadd_rn(s, my[(768 + (cw[r] >> 24)) * 32]);
+            float s = my[(cw[r] & 0xFFu) * 64];
+            s = __fadd_rn(s, my[((cw[r] >> 8) & 0xFFu) * 64 + 32]);
+            s = __fadd_rn(s, my[16384 + ((cw[r] >> 16) & 0xFFu) * 64]);
+            s = __fadd_rn(s, my[16384 + (cw[r] >> 24) * 64 + 32]);
             acc[r] = s;
         }
 #pragma unroll

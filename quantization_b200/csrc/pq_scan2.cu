@@ -57,6 +57,63 @@ __device__ __forceinline__ void pq2_tma_tile(void *dst, const CUtensorMap *map, 
         : "memory");
 }
 
+// One LUT gather.  The slice's entry (b, code) of lane w's column sits at byte
+//   (b >> 1) * 65536 + code * 256 + (b & 1) * 128 + w * 4        (pq.cu pq_lut_permute_kernel)
+// so the variable part of the address, code << 8 | w * 4, is ONE byte permute of the code word with a per-lane
+// constant, and the rest is the load's immediate.  FAST: the per-lane constant also carries the upper half of the
+// LUT's shared-memory address and the immediate its bits 8..15 (kPq2LutBase: user shared memory starts 1 KiB into
+// the CTA's window on sm_100), which leaves no add at all; the kernel checks the address and takes the other
+// form (one add per gather) if the assumption does not hold.
+constexpr uint32_t kPq2LutBase = 0x400;
+template <bool FAST, int B>
+__device__ __forceinline__ float pq2_gather(uint32_t cw, uint32_t lane_const, uint32_t lut_s) {
+    float v;
+    if (FAST) {
+        const uint32_t a = __byte_perm(cw, lane_const, 0x7604 | (B << 4));
+        asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(a), "n"(kPq2LutBase + (B >> 1) * 65536 + (B & 1) * 128));
+    } else {
+        const uint32_t a = lut_s + __byte_perm(cw, lane_const, 0x5504 | (B << 4));
+        asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(a), "n"((B >> 1) * 65536 + (B & 1) * 128));
+    }
+    return v;
+}
+
+// 16 rows x 128 chunks of one warp: gathers, per-lane sums, transposing butterfly.  Lanes 2j and 2j+1 return the
+// slice sum of row j.
+template <bool FAST>
+__device__ __forceinline__ float pq2_rows16(const uint32_t (&cw)[16], uint32_t lane_const, uint32_t lut_s, uint32_t lane) {
+    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2;
+    float a[16];
+#pragma unroll
+    for (int r = 0; r < 16; r++) {
+        float v = pq2_gather<FAST, 0>(cw[r], lane_const, lut_s);
+        v = __fadd_rn(v, pq2_gather<FAST, 1>(cw[r], lane_const, lut_s));
+        v = __fadd_rn(v, pq2_gather<FAST, 2>(cw[r], lane_const, lut_s));
+        v = __fadd_rn(v, pq2_gather<FAST, 3>(cw[r], lane_const, lut_s));
+        a[r] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        float keep = upper16 ? a[i + 8] : a[i], send = upper16 ? a[i] : a[i + 8];
+        a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 16));
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        float keep = upper8 ? a[i + 4] : a[i], send = upper8 ? a[i] : a[i + 4];
+        a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 8));
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        float keep = upper4 ? a[i + 2] : a[i], send = upper4 ? a[i] : a[i + 2];
+        a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 4));
+    }
+    {
+        float keep = upper2 ? a[1] : a[0], send = upper2 ? a[0] : a[1];
+        a[0] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 2));
+    }
+    return __fadd_rn(a[0], __shfl_xor_sync(0xffffffffu, a[0], 1));
+}
+
 __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_constant__ CUtensorMap map, const PqScan2Params p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     float *slut = reinterpret_cast<float *>(smem);
@@ -110,8 +167,10 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
 
     // ---------------- consumers ----------------
     const uint32_t group = warp / (kPq2Warps / kPq2Groups), member = warp % (kPq2Warps / kPq2Groups);
-    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2;
-    const char *my = reinterpret_cast<const char *>(slut + lane);
+    const uint32_t lut_s = smem_u32(slut);
+    const bool fast = (lut_s & 0xFFFFu) == kPq2LutBase;
+    const uint32_t lane_const = fast ? ((lut_s & 0xFFFF0000u) | lane * 4u) : lane * 4u;
+    const uint32_t slot_mask = p.n_slots - 1, slot_shift = 31 - __clz(p.n_slots);  // n_slots is a power of two
     uint32_t seq = 0;       // tiles issued by the producer before the current (block, slice)
     uint32_t lut_phase = 0;
     for (uint32_t lb = 0; lb < my_blocks; lb++) {
@@ -131,7 +190,7 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
             mbar_wait(lutbar, lut_phase);
             lut_phase ^= 1;
             for (uint32_t t = group; t < tiles_pb; t += kPq2Groups) {
-                const uint32_t T = seq + t, slot = T % p.n_slots, use = T / p.n_slots;
+                const uint32_t T = seq + t, slot = T & slot_mask, use = T >> slot_shift;
                 mbar_wait(&full[slot], use & 1);
                 const uint32_t *tile = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * kPq2TileBytes);
                 uint32_t cw[16];
@@ -139,37 +198,7 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
                 for (int r = 0; r < 16; r++) cw[r] = tile[(member * 16 + r) * 32 + lane];
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty[slot]);  // the codes are in registers: the slot can be refilled
-                float a[16];
-#pragma unroll
-                for (int r = 0; r < 16; r++) {
-                    // one PRMT (byte extract) + one scaled add per gather address; entry (b, code) of this lane's
-                    // column sits at byte (b*256 + code) * 128 + lane * 4
-                    float v = *reinterpret_cast<const float *>(my + __byte_perm(cw[r], 0, 0x4440) * 128u);
-                    v = __fadd_rn(v, *reinterpret_cast<const float *>(my + 32768 + __byte_perm(cw[r], 0, 0x4441) * 128u));
-                    v = __fadd_rn(v, *reinterpret_cast<const float *>(my + 65536 + __byte_perm(cw[r], 0, 0x4442) * 128u));
-                    v = __fadd_rn(v, *reinterpret_cast<const float *>(my + 98304 + __byte_perm(cw[r], 0, 0x4443) * 128u));
-                    a[r] = v;
-                }
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    float keep = upper16 ? a[i + 8] : a[i], send = upper16 ? a[i] : a[i + 8];
-                    a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 16));
-                }
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    float keep = upper8 ? a[i + 4] : a[i], send = upper8 ? a[i] : a[i + 4];
-                    a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 8));
-                }
-#pragma unroll
-                for (int i = 0; i < 2; i++) {
-                    float keep = upper4 ? a[i + 2] : a[i], send = upper4 ? a[i] : a[i + 2];
-                    a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 4));
-                }
-                {
-                    float keep = upper2 ? a[1] : a[0], send = upper2 ? a[0] : a[1];
-                    a[0] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 2));
-                }
-                const float total = __fadd_rn(a[0], __shfl_xor_sync(0xffffffffu, a[0], 1));
+                const float total = fast ? pq2_rows16<true>(cw, lane_const, lut_s, lane) : pq2_rows16<false>(cw, lane_const, lut_s, lane);
                 if (!(lane & 1)) {
                     const uint32_t r = t * kPq2TileRows + member * 16 + (lane >> 1);
                     acc[r] = s == 0 ? total : __fadd_rn(acc[r], total);  // slice order: ((p0 + p1) + p2) + ...
@@ -282,9 +311,8 @@ bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32
     // n_slots must be a multiple of the group count: a slot then always serves the same warp group, so no waiter
     // can be two phases ahead of a slot's mbarrier (with 6 slots a fast group passed the parity wait of a tile two
     // fills ahead while the other group's fill was still in flight: launch failure, mbarrier over-arrival)
-    p.n_slots = env_slots ? env_slots / kPq2Groups * kPq2Groups : 8;
-    if (p.n_slots == 0) p.n_slots = kPq2Groups;
-    if (p.n_slots > 8) p.n_slots = 8;
+    // and a power of two (the slot of a tile is a mask of its sequence number)
+    p.n_slots = env_slots == 4 ? 4 : 8;
     const size_t fixed = (size_t)kPq2SliceFloats * 4 + (size_t)p.n_slots * kPq2TileBytes + (2 * p.n_slots + 1) * 8 + 128 * 8 + 16 + 1024;
     const uint32_t max_block = (uint32_t)((ctx->smem_optin - fixed) / 4 / kPq2TileRows * kPq2TileRows);
     // one block per CTA when the corpus is small enough for that, else blocks of the largest size that fits
