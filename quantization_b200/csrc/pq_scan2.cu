@@ -78,40 +78,27 @@ __device__ __forceinline__ float pq2_gather(uint32_t cw, uint32_t lane_const, ui
     return v;
 }
 
-// 16 rows x 128 chunks of one warp: gathers, per-lane sums, transposing butterfly.  Lanes 2j and 2j+1 return the
-// slice sum of row j.
+// 16 rows x 128 chunks of one warp.  Lane L works on ONE row (L & 15) and on the 16 code words 16*(L >> 4) ..+15 of
+// it, in the order word = 16*(L >> 4) + ((L & 15) ^ j), j = 0..15: at every step the 32 lanes read 32 different word
+// columns (code loads and LUT gathers both conflict free), and a row's 128 lookups are spread over just two lanes,
+// so the whole cross-lane reduction is one shuffle (the first version gave each lane one column of all 16 rows and
+// paid a 16-value transposing butterfly: 16 shuffles + 30 selects per 16 rows, on the same pipe as the gathers).
+// lc0 = the lane constant of pq2_gather for j = 0; step j uses lc0 ^ 4j.  Returns the row's slice sum.
 template <bool FAST>
-__device__ __forceinline__ float pq2_rows16(const uint32_t (&cw)[16], uint32_t lane_const, uint32_t lut_s, uint32_t lane) {
-    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2;
-    float a[16];
+__device__ __forceinline__ float pq2_rows16(const uint32_t (&cw)[16], uint32_t lc0, uint32_t lut_s) {
+    float s0, s1, s2, s3;
 #pragma unroll
-    for (int r = 0; r < 16; r++) {
-        float v = pq2_gather<FAST, 0>(cw[r], lane_const, lut_s);
-        v = __fadd_rn(v, pq2_gather<FAST, 1>(cw[r], lane_const, lut_s));
-        v = __fadd_rn(v, pq2_gather<FAST, 2>(cw[r], lane_const, lut_s));
-        v = __fadd_rn(v, pq2_gather<FAST, 3>(cw[r], lane_const, lut_s));
-        a[r] = v;
+    for (int j = 0; j < 16; j++) {
+        const uint32_t lc = lc0 ^ (4u * j);
+        const float g0 = pq2_gather<FAST, 0>(cw[j], lc, lut_s), g1 = pq2_gather<FAST, 1>(cw[j], lc, lut_s);
+        const float g2 = pq2_gather<FAST, 2>(cw[j], lc, lut_s), g3 = pq2_gather<FAST, 3>(cw[j], lc, lut_s);
+        s0 = j ? __fadd_rn(s0, g0) : g0;
+        s1 = j ? __fadd_rn(s1, g1) : g1;
+        s2 = j ? __fadd_rn(s2, g2) : g2;
+        s3 = j ? __fadd_rn(s3, g3) : g3;
     }
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-        float keep = upper16 ? a[i + 8] : a[i], send = upper16 ? a[i] : a[i + 8];
-        a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 16));
-    }
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        float keep = upper8 ? a[i + 4] : a[i], send = upper8 ? a[i] : a[i + 4];
-        a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 8));
-    }
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-        float keep = upper4 ? a[i + 2] : a[i], send = upper4 ? a[i] : a[i + 2];
-        a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 4));
-    }
-    {
-        float keep = upper2 ? a[1] : a[0], send = upper2 ? a[0] : a[1];
-        a[0] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 2));
-    }
-    return __fadd_rn(a[0], __shfl_xor_sync(0xffffffffu, a[0], 1));
+    const float s = __fadd_rn(__fadd_rn(s0, s2), __fadd_rn(s1, s3));
+    return __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, 16));
 }
 
 __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_constant__ CUtensorMap map, const PqScan2Params p) {
@@ -169,7 +156,9 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
     const uint32_t group = warp / (kPq2Warps / kPq2Groups), member = warp % (kPq2Warps / kPq2Groups);
     const uint32_t lut_s = smem_u32(slut);
     const bool fast = (lut_s & 0xFFFFu) == kPq2LutBase;
-    const uint32_t lane_const = fast ? ((lut_s & 0xFFFF0000u) | lane * 4u) : lane * 4u;
+    const uint32_t rsub = lane & 15u;                                  // this lane's row within the warp's 16
+    const uint32_t col0 = (lane & 16u) + rsub;                          // its word column at step 0
+    const uint32_t lc0 = (fast ? (lut_s & 0xFFFF0000u) : 0u) | col0 * 4u;
     const uint32_t slot_mask = p.n_slots - 1, slot_shift = 31 - __clz(p.n_slots);  // n_slots is a power of two
     uint32_t seq = 0;       // tiles issued by the producer before the current (block, slice)
     uint32_t lut_phase = 0;
@@ -193,14 +182,16 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
                 const uint32_t T = seq + t, slot = T & slot_mask, use = T >> slot_shift;
                 mbar_wait(&full[slot], use & 1);
                 const uint32_t *tile = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * kPq2TileBytes);
+                const char *tile_row = reinterpret_cast<const char *>(tile) + (member * 16 + rsub) * 128;
                 uint32_t cw[16];
 #pragma unroll
-                for (int r = 0; r < 16; r++) cw[r] = tile[(member * 16 + r) * 32 + lane];
+                for (int j = 0; j < 16; j++)
+                    cw[j] = *reinterpret_cast<const uint32_t *>(tile_row + ((lc0 ^ (4u * j)) & 0x7Cu));
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty[slot]);  // the codes are in registers: the slot can be refilled
-                const float total = fast ? pq2_rows16<true>(cw, lane_const, lut_s, lane) : pq2_rows16<false>(cw, lane_const, lut_s, lane);
-                if (!(lane & 1)) {
-                    const uint32_t r = t * kPq2TileRows + member * 16 + (lane >> 1);
+                const float total = fast ? pq2_rows16<true>(cw, lc0, lut_s) : pq2_rows16<false>(cw, lc0, lut_s);
+                if (lane < 16) {
+                    const uint32_t r = t * kPq2TileRows + member * 16 + rsub;
                     acc[r] = s == 0 ? total : __fadd_rn(acc[r], total);  // slice order: ((p0 + p1) + p2) + ...
                 }
             }
