@@ -101,6 +101,22 @@ __device__ __forceinline__ float pq2_rows16(const uint32_t (&cw)[16], uint32_t l
     return __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, 16));
 }
 
+// position of a producer lane in its group's tile sequence: t = lane, lane + 4, ... of every (block, slice)
+struct Pq2Cursor {
+    uint32_t lb, s, t;
+    __device__ __forceinline__ bool valid(uint32_t my_blocks) const { return lb < my_blocks; }
+    __device__ __forceinline__ void next(uint32_t tiles_pb, uint32_t n_slices, uint32_t g) {
+        t += kPq2Groups;
+        if (t >= tiles_pb) {
+            t = g;
+            if (++s == n_slices) {
+                s = 0;
+                lb++;
+            }
+        }
+    }
+};
+
 __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_constant__ CUtensorMap map, const PqScan2Params p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     float *slut = reinterpret_cast<float *>(smem);
@@ -129,24 +145,23 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
     const uint32_t my_blocks = blockIdx.x < p.n_blocks ? (p.n_blocks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
     if (warp == kPq2Warps) {
-        // ---------------- producer ----------------
-        if (lane == 0) {
-            uint32_t slot = 0, round = 0;
-            for (uint32_t lb = 0; lb < my_blocks; lb++) {
-                const uint64_t row0 = (uint64_t)(blockIdx.x + lb * gridDim.x) * p.block_rows;
-                for (uint32_t s = 0; s < p.n_slices; s++) {
-                    for (uint32_t t = 0; t < tiles_pb; t++) {
-                        if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
-                        mbar_arrive_expect_tx(&full[slot], kPq2TileBytes);
-                        // rows past `count` are out of bounds for the tensor map: zero filled, never stored
-                        pq2_tma_tile(ring + (size_t)slot * kPq2TileBytes, &map, (int32_t)(s * kPq2SliceChunks),
-                                     (int32_t)(row0 + (uint64_t)t * kPq2TileRows), &full[slot]);
-                        if (++slot == p.n_slots) {
-                            slot = 0;
-                            round++;
-                        }
-                    }
-                }
+        // ---------------- producers ----------------
+        // Lane g streams the tiles of consumer group g (t = g, g + 4, ... of every (block, slice)) through the group's
+        // own two slots, g and g + 4: the groups' pipelines are independent, so a group that falls behind does not
+        // hold back the loads of the others, and a slot only ever serves one group, whatever the tile count.
+        // (Pulling tiles into L2 ahead of the ring with cp.async.bulk.prefetch.tensor made the scan 14 % slower; launching
+        // this kernel as a programmatic dependent of the LUT permutation changed nothing measurable.)
+        if (lane < kPq2Groups && lane < tiles_pb) {
+            Pq2Cursor cur{0, 0, lane};
+            for (uint32_t n = 0; cur.valid(my_blocks); n++) {
+                const uint32_t slot = lane + kPq2Groups * (n & 1), use = n >> 1;
+                if (use > 0) mbar_wait(&empty[slot], (use - 1) & 1);
+                mbar_arrive_expect_tx(&full[slot], kPq2TileBytes);
+                // rows past `count` are out of bounds for the tensor map: zero filled, never stored
+                pq2_tma_tile(ring + (size_t)slot * kPq2TileBytes, &map, (int32_t)(cur.s * kPq2SliceChunks),
+                             (int32_t)((uint64_t)(blockIdx.x + cur.lb * gridDim.x) * p.block_rows + (uint64_t)cur.t * kPq2TileRows),
+                             &full[slot]);
+                cur.next(tiles_pb, p.n_slices, lane);
             }
         }
         return;
@@ -159,12 +174,11 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
     const uint32_t rsub = lane & 15u;                                  // this lane's row within the warp's 16
     const uint32_t col0 = (lane & 16u) + rsub;                          // its word column at step 0
     const uint32_t lc0 = (fast ? (lut_s & 0xFFFF0000u) : 0u) | col0 * 4u;
-    const uint32_t slot_mask = p.n_slots - 1, slot_shift = 31 - __clz(p.n_slots);  // n_slots is a power of two
-    uint32_t seq = 0;       // tiles issued by the producer before the current (block, slice)
+    uint32_t n = 0;         // tiles this warp's group has consumed (the group's slots alternate: group, group + 4)
     uint32_t lut_phase = 0;
     for (uint32_t lb = 0; lb < my_blocks; lb++) {
         const uint64_t row0 = (uint64_t)(blockIdx.x + lb * gridDim.x) * p.block_rows;
-        for (uint32_t s = 0; s < p.n_slices; s++, seq += tiles_pb) {
+        for (uint32_t s = 0; s < p.n_slices; s++) {
             // every consumer is done with the previous slice's LUT (and, at s == 0, has stored the previous block)
             // (the top-k phase writes candidate keys into the LUT area with ordinary stores: order them before the
             // bulk copy's writes)
@@ -178,8 +192,8 @@ __global__ void __launch_bounds__(kPq2Threads, 1) pq_scan2_kernel(const __grid_c
             }
             mbar_wait(lutbar, lut_phase);
             lut_phase ^= 1;
-            for (uint32_t t = group; t < tiles_pb; t += kPq2Groups) {
-                const uint32_t T = seq + t, slot = T & slot_mask, use = T >> slot_shift;
+            for (uint32_t t = group; t < tiles_pb; t += kPq2Groups, n++) {
+                const uint32_t slot = group + kPq2Groups * (n & 1), use = n >> 1;
                 mbar_wait(&full[slot], use & 1);
                 const uint32_t *tile = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * kPq2TileBytes);
                 const char *tile_row = reinterpret_cast<const char *>(tile) + (member * 16 + rsub) * 128;
@@ -298,12 +312,8 @@ bool pq_scan2_launch(qz_ctx *ctx, const uint8_t *d_codes, uint64_t count, uint32
     p.k = k ? k : 1;
     p.flip = largest ? 0u : 0xFFFFFFFFu;
     p.id_base = id_base;
-    const uint32_t env_slots = tune_u32("QZ_PQ_SLOTS", 0), env_block = tune_u32("QZ_PQ_BLOCK_ROWS", 0);
-    // n_slots must be a multiple of the group count: a slot then always serves the same warp group, so no waiter
-    // can be two phases ahead of a slot's mbarrier (with 6 slots a fast group passed the parity wait of a tile two
-    // fills ahead while the other group's fill was still in flight: launch failure, mbarrier over-arrival)
-    // and a power of two (the slot of a tile is a mask of its sequence number)
-    p.n_slots = env_slots == 4 ? 4 : 8;
+    const uint32_t env_block = tune_u32("QZ_PQ_BLOCK_ROWS", 0);
+    p.n_slots = 2 * kPq2Groups;  // two slots per consumer group (producer lanes in the kernel)
     const size_t fixed = (size_t)kPq2SliceFloats * 4 + (size_t)p.n_slots * kPq2TileBytes + (2 * p.n_slots + 1) * 8 + 128 * 8 + 16 + 1024;
     const uint32_t max_block = (uint32_t)((ctx->smem_optin - fixed) / 4 / kPq2TileRows * kPq2TileRows);
     // one block per CTA when the corpus is small enough for that, else blocks of the largest size that fits
