@@ -78,6 +78,22 @@ QZ_API int32_t qz_ctx_sm_count(const qz_ctx *ctx);
  * since qz_ctx_set_timing (the benchmark's roofline measurement). */
 QZ_API qz_status qz_ctx_set_timing(qz_ctx *ctx, int32_t enabled);
 QZ_API qz_status qz_ctx_get_timing(qz_ctx *ctx, double *total_ms, uint64_t *launches);
+/* Chained scans.  Consecutive qz_scan_topk_dev / qz_scan_topk_peer_dev / qz_scan_topk_gather_dev calls (u8 and binary,
+ * k <= 128) on a context are launched so that the streaming of query i+1 overlaps the final merge of query i
+ * (programmatic dependent launch; results and their order on the stream are unchanged).  That is only safe when no
+ * other work can sit between two scans on the stream, so it is automatic for a context that owns its stream
+ * (qz_ctx_create with stream = NULL) and needs this promise for a caller-provided stream: while it is on, anything
+ * the caller enqueues on that stream between two scans that WRITES the encoded query or the index storage must be
+ * followed by an event wait or another non-kernel operation (which ends a chain).  Default off. */
+QZ_API qz_status qz_ctx_set_scan_chaining(qz_ctx *ctx, int32_t enabled);
+/* Optional: per-CTA phase stamps of the u8 / binary scan kernel.  d_stamps = device buffer of
+ * QZ_STAMP_WORDS u64 per SM (qz_ctx_sm_count), or NULL to switch the stamps off.  Every CTA of the next scans
+ * writes, at [blockIdx][i]: 0 globaltimer (ns) at kernel entry, 1 clock64 at entry, 2 clock64 after the top-k
+ * warm-up, 3 after its last tile, 4 after its list is published, 5 / 6 (last CTA only, else 0) after the final
+ * merge / after the peer exchange, 7 globaltimer at exit.  Profiling aid (tools/phase_stamps.py); no reference
+ * counterpart. */
+#define QZ_STAMP_WORDS 8
+QZ_API qz_status qz_ctx_set_phase_stamps(qz_ctx *ctx, uint64_t *d_stamps);
 
 /* ---- u8 scalar quantizer (EncodedVectorsU8, encoded_vectors_u8.rs) ------------------------- */
 

@@ -27,6 +27,8 @@ _SIGS = {
     "qz_ctx_sm_count": (C.c_int32, [vp]),
     "qz_ctx_set_timing": (C.c_int32, [vp, C.c_int32]),
     "qz_ctx_get_timing": (C.c_int32, [vp, C.POINTER(C.c_double), u64p]),
+    "qz_ctx_set_phase_stamps": (C.c_int32, [vp, vp]),
+    "qz_ctx_set_scan_chaining": (C.c_int32, [vp, C.c_int32]),
     "qz_u8_actual_dim": (C.c_uint32, [C.c_uint32]),
     "qz_u8_row_bytes": (C.c_uint32, [C.c_uint32]),
     "qz_u8_index_create": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.c_int32, C.c_float, C.c_float,

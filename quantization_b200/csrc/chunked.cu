@@ -46,6 +46,7 @@ qz_status qz_scan_topk_chunked(qz_index *a, qz_index *b, const uint8_t *host_sto
     if (n_out) *n_out = 0;
     if (count == 0) return QZ_OK;
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const uint64_t cap = a->count, row = a->row_bytes;
     const uint64_t n_chunks = (count + cap - 1) / cap;

@@ -42,6 +42,7 @@ qz_status qz_peer_create(qz_ctx *ctx, uint32_t world, uint32_t rank, uint8_t *ha
     if (world < 1 || world > (uint32_t)kMaxPeers || rank >= world)
         return fail(ctx, QZ_ARGUMENTS, "qz_peer_create: world must be 1..8 and rank < world");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     qz_peer *pe = new qz_peer();
     pe->ctx = ctx;
@@ -68,6 +69,7 @@ qz_status qz_peer_connect(qz_peer *pe, const uint8_t *all_handles) {
     if (!pe || !all_handles) return QZ_ARGUMENTS;
     qz_ctx *ctx = pe->ctx;
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     for (uint32_t r = 0; r < pe->world; r++) {
         if (r == pe->rank || pe->mapped[r]) continue;
@@ -173,6 +175,7 @@ static qz_status search_topk_exchange(qz_index *ix, qz_peer *pe, int32_t root, c
     const size_t qb = qz_query_bytes(ix), fb = (size_t)ix->dim * sizeof(float);
     if (!fb || !qb) return fail(ctx, QZ_ARGUMENTS, "search_topk_peer: dim 0");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t fb_pad = (fb + 255) / 256 * 256, qb_pad = (qb + 255) / 256 * 256;
     QZ_TRY(ensure_query(ctx, fb_pad + qb_pad + 16));

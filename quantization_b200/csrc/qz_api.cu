@@ -72,6 +72,7 @@ qz_status qz_u8_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t count
     if (dim == 0) return fail(ctx, QZ_ARGUMENTS, "qz_u8_index_create: dim is 0");
     if (count + id_base > 0xFFFFFFFEull) return fail(ctx, QZ_ARGUMENTS, "qz_u8_index_create: point ids exceed u32");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     qz_index *ix = new qz_index();
     ix->ctx = ctx;
@@ -140,6 +141,7 @@ qz_status qz_index_download(qz_index *ix, uint8_t *storage) {
     if (bad_index(ix) || !storage) return QZ_ARGUMENTS;
     qz_ctx *ctx = ix->ctx;
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     QZ_CUDA(ctx, cudaMemcpyAsync(storage, ix->d_storage, (size_t)ix->count * ix->row_bytes, cudaMemcpyDeviceToHost,
                                  ctx->stream));
@@ -161,6 +163,7 @@ qz_status qz_encode_query(qz_index *ix, const float *query, void *out) {
     if (!query || !out) return fail(ix->ctx, QZ_ARGUMENTS, "encode_query: NULL");
     qz_ctx *ctx = ix->ctx;
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t qb = qz_query_bytes(ix), fb = (size_t)ix->dim * sizeof(float);
     const size_t fb_pad = (fb + 255) / 256 * 256;
@@ -198,6 +201,7 @@ qz_status qz_scan_topk(qz_index *ix, const void *enc_query, uint32_t k, int32_t 
     if (!scores || !ids) return fail(ctx, QZ_ARGUMENTS, "scan_topk: NULL output");
     if (k == 0 || k > QZ_MAX_K) return fail(ctx, QZ_ARGUMENTS, "scan_topk: k must be in [1, QZ_MAX_K]");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t qb = qz_query_bytes(ix), qb_pad = (qb + 255) / 256 * 256;
     if (qb && !enc_query) return fail(ctx, QZ_ARGUMENTS, "scan_topk: NULL query");
@@ -230,6 +234,7 @@ qz_status qz_search_topk(qz_index *ix, const float *query, uint32_t k, int32_t l
     const size_t qb = qz_query_bytes(ix), fb = (size_t)ix->dim * sizeof(float);
     if (fb && !query) return fail(ctx, QZ_ARGUMENTS, "search_topk: NULL query");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t fb_pad = (fb + 255) / 256 * 256, qb_pad = (qb + 255) / 256 * 256;
     QZ_TRY(ensure_query(ctx, fb_pad + qb_pad + 16));
@@ -267,6 +272,7 @@ qz_status qz_scan_scores(qz_index *ix, const void *enc_query, float *scores) {
     if (ix->count == 0) return QZ_OK;
     if (!scores) return fail(ctx, QZ_ARGUMENTS, "scan_scores: NULL output");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t qb = qz_query_bytes(ix), qb_pad = (qb + 255) / 256 * 256;
     if (qb && !enc_query) return fail(ctx, QZ_ARGUMENTS, "scan_scores: NULL query");
@@ -310,6 +316,7 @@ static qz_status score_ids_common(qz_index *ix, const void *enc_query, const uin
         if (rows_b[i] >= ix->count || (pairs && rows_a[i] >= ix->count))
             return fail(ctx, QZ_ARGUMENTS, "score: row index out of range");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t qb = pairs ? 0 : qz_query_bytes(ix), qb_pad = (qb + 255) / 256 * 256;
     if (qb && !enc_query) return fail(ctx, QZ_ARGUMENTS, "score: NULL query");
@@ -396,6 +403,7 @@ qz_status qz_bin_index_create(qz_ctx *ctx, const uint8_t *storage, uint64_t coun
         return fail(ctx, QZ_ARGUMENTS, "qz_bin_index_create: store_bytes must be 1 (u8) or 16 (u128)");
     if (count + id_base > 0xFFFFFFFEull) return fail(ctx, QZ_ARGUMENTS, "qz_bin_index_create: point ids exceed u32");
     std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_tail = 0;  // host-buffer entry points copy and synchronise: never part of a scan chain
     QZ_CUDA(ctx, cudaSetDevice(ctx->device));
     qz_index *ix = new qz_index();
     ix->ctx = ctx;

@@ -196,6 +196,21 @@ qz_status qz_ctx_set_timing(qz_ctx *ctx, int32_t enabled) {
     return QZ_OK;
 }
 
+qz_status qz_ctx_set_scan_chaining(qz_ctx *ctx, int32_t enabled) {
+    if (!ctx) return QZ_ARGUMENTS;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->chain_ok = enabled != 0;
+    ctx->chain_tail = 0;
+    return QZ_OK;
+}
+
+qz_status qz_ctx_set_phase_stamps(qz_ctx *ctx, uint64_t *d_stamps) {
+    if (!ctx) return QZ_ARGUMENTS;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->d_stamps = d_stamps;
+    return QZ_OK;
+}
+
 qz_status qz_ctx_get_timing(qz_ctx *ctx, double *total_ms, uint64_t *launches) {
     if (!ctx) return QZ_ARGUMENTS;
     timing_drain(ctx, true);

@@ -41,6 +41,14 @@ struct qz_ctx {
     cudaEvent_t ev_start[kTimingRing] = {}, ev_stop[kTimingRing] = {};
     uint64_t ev_head = 0, ev_tail = 0;  // [tail, head) pairs are recorded and not yet read
     double timed_ms = 0.0;
+    // Chained scans (row_scan.cu): a fused top-k scan launched right behind another one of this context may start
+    // while the previous one's last CTA is still merging (programmatic dependent launch).  Eligible when nothing
+    // else can have been enqueued between the two: the context owns its stream, or the caller said so
+    // (qz_ctx_set_scan_chaining), and no other kernel of this library was launched in between.
+    bool chain_ok = false;      // caller's promise for a stream the context does not own
+    uint64_t chain_tail = 0;    // value of `launches` right after the last chainable scan launch, 0 = none
+    bool pdl_next = false;      // launch_one: give the next launch the programmatic-serialization attribute
+    uint64_t *d_stamps = nullptr;  // qz_ctx_set_phase_stamps: [sm_count][QZ_STAMP_WORDS], or NULL
     uint64_t timed_n = 0;
     // One-time kernel attribute setup.  cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies to the CURRENT
     // device only, so "done" is a property of the context (= device), never of the process: a host that creates

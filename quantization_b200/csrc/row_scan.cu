@@ -132,6 +132,7 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     p.Kp = Kp;
     p.flip = largest ? 0u : 0xFFFFFFFFu;
     p.id_base = ix->id_base;
+    p.stamps = ctx->d_stamps;
     uint32_t grid = pl.n_tiles < (uint32_t)ctx->sm_count ? pl.n_tiles : (uint32_t)ctx->sm_count;
     if (fin) *fin->fused = false;
     const bool env_nofuse = tune_flag("QZ_SCAN_NO_FUSED_MERGE");
@@ -168,6 +169,10 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     }
     if (fin && fin->px && !*fin->fused)
         return fail(ctx, QZ_ARGUMENTS, "peer exchange needs the in-launch merge (k <= 128, streaming row shape)");
+    // chained launch: see qz_ctx::chain_tail.  The kernel reads nothing a previous scan writes before its
+    // griddepcontrol.wait (query and storage are inputs of both), so only the tail of the previous scan overlaps.
+    const bool chainable = fin && *fin->fused && !ctx->timing && (ctx->own_stream || ctx->chain_ok);
+    ctx->pdl_next = chainable && ctx->chain_tail != 0 && ctx->chain_tail == ctx->launches;
     cudaError_t e;
     timing_begin(ctx);
     if (ix->codec == QZ_CODEC_BIN && pl.vec) e = launch_row_scan_xorv(ctx, pl.lpr, pl.wpl, pl.full, p, grid, pl.smem);
@@ -175,10 +180,13 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     else if (ix->distance == QZ_L1) e = launch_row_scan_l1(ctx, pl.wpl, pl.full, p, grid, pl.smem);
     else e = launch_row_scan_dot(ctx, pl.wpl, pl.full, p, grid, pl.smem);
     timing_end(ctx);
+    ctx->pdl_next = false;
+    ctx->chain_tail = 0;
     if (e == cudaErrorInvalidValue && !ctx->err.empty() && ctx->err.find("cudaFuncSetAttribute") != std::string::npos)
         return QZ_ENCODING;  // ensure_smem_attr failed and left its message
     if (e != cudaSuccess) return cuda_fail(ctx, e, "row_scan_kernel launch");
     ctx->launches++;
+    if (chainable) ctx->chain_tail = ctx->launches;
     if (n_lists) *n_lists = grid;
     if (Kp_out) *Kp_out = Kp;
     return QZ_OK;

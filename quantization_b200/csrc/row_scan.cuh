@@ -65,7 +65,18 @@ struct RowScanParams {
     uint32_t *done;  // zero before the launch; the last CTA leaves it zero again
     MergeParams merge;
     PeerExchange px;  // px.world > 1: merge.keys points at this GPU's own gather slot; see PeerExchange
+    uint64_t *stamps;  // optional [gridDim.x][QZ_STAMP_WORDS] phase stamps (qz_ctx_set_phase_stamps)
 };
+
+__device__ __forceinline__ uint64_t global_ns() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// thread `who` of the CTA records phase i (no-op without a stamp buffer)
+__device__ __forceinline__ void stamp(const RowScanParams &p, int i, bool who, bool wall = false) {
+    if (p.stamps && who) p.stamps[(size_t)blockIdx.x * QZ_STAMP_WORDS + i] = wall ? global_ns() : (uint64_t)clock64();
+}
 
 template <int OP>
 __device__ __forceinline__ uint32_t scan_op(uint32_t v, uint32_t q, uint32_t acc) {
@@ -89,6 +100,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool do_topk = p.partial != nullptr;
+    stamp(p, 0, threadIdx.x == 0, true);
+    stamp(p, 1, threadIdx.x == 0);
+    if (p.stamps && threadIdx.x < 2) p.stamps[(size_t)blockIdx.x * QZ_STAMP_WORDS + 5 + threadIdx.x] = 0;
     const uint32_t n_slots = p.n_slots, n_groups = p.n_groups;
     const uint32_t warps_per_slot = kConsumerWarps / n_groups;  // warps that share a tile
 
@@ -104,6 +118,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     if (do_topk)
         for (uint32_t i = threadIdx.x; i < p.Kp; i += blockDim.x) top[i] = 0;
     __syncthreads();
+    // A scan launched behind this one as a programmatic dependent (row_scan.cu, chained launches) may take the SMs
+    // this grid's CTAs leave while the last CTA is still merging; it waits for this grid to complete before it
+    // touches anything shared with it (griddepcontrol.wait below).
+    if (p.done) asm volatile("griddepcontrol.launch_dependents;");
 
     // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...; local tile t lives in slot t % n_slots
     const uint32_t my_tiles = (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
@@ -199,6 +217,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
                 if (lane == 0) *thr = top[p.k - 1];
             }
             named_bar_sync(1, kConsumerWarps * 32);
+            stamp(p, 2, threadIdx.x == 0);
             warm = false;
         }
         if (t >= my_tiles) {
@@ -326,6 +345,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
 
     if (do_topk) {
         __syncwarp();
+        stamp(p, 3, threadIdx.x == 0);
         if (coop) {
             // every warp pads its leftovers to a full chunk; the 16 chunks are reduced together
             for (int i = cnt + lane; i < kCandPerWarp; i += 32) cand[i] = 0ull;
@@ -346,8 +366,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             cta_topk_flush(st, cand, cnt, lane);
         }
         named_bar_sync(1, kConsumerWarps * 32);
+        // the per-CTA lists, the arrival counter, the output buffers and the peer slots are shared with the previous
+        // scan of a chain: it must be complete (no-op for an ordinary launch)
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         uint64_t *out = p.partial + (size_t)blockIdx.x * p.Kp;
         for (uint32_t i = threadIdx.x; i < p.Kp; i += kConsumerWarps * 32) out[i] = top[i];
+        stamp(p, 4, threadIdx.x == 0);
         if (p.done) {
             // last-CTA-done: publish this list, count, and let the last arrival merge them all.  Every bulk copy
             // of this CTA has been consumed, so the ring is free to serve as the merge's work area.
@@ -366,10 +390,13 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             if (is_last) {
                 prune_merge<1, true>(p.merge, reinterpret_cast<uint64_t *>(ring), threadIdx.x, kConsumerWarps * 32);
                 if (threadIdx.x == 0) *p.done = 0;
+                stamp(p, 5, threadIdx.x == 0);
                 if (p.px.world > 1) peer_exchange_merge(p.px, p.k, reinterpret_cast<uint64_t *>(ring));
+                stamp(p, 6, threadIdx.x == 0);
             }
         }
     }
+    stamp(p, 7, threadIdx.x == 0, true);
 }
 
 }  // namespace qz

@@ -10,8 +10,22 @@ template <int OP, int WPL, bool FULL>
 static cudaError_t launch_one(qz_ctx *ctx, const RowScanParams &p, uint32_t grid, size_t smem) {
     if (ensure_smem_attr(ctx, (const void *)row_scan_kernel<OP, WPL, FULL>, 227 * 1024) != QZ_OK)
         return cudaErrorInvalidValue;  // (text already in ctx->err)
-    row_scan_kernel<OP, WPL, FULL><<<grid, kScanThreads, smem, ctx->stream>>>(p);
-    return cudaGetLastError();
+    if (!ctx->pdl_next) {
+        row_scan_kernel<OP, WPL, FULL><<<grid, kScanThreads, smem, ctx->stream>>>(p);
+        return cudaGetLastError();
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kScanThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, row_scan_kernel<OP, WPL, FULL>, p);
+    return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 // wpl must come from row_scan_wpl(); `full` = code_words == 32 * wpl

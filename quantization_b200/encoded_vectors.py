@@ -130,6 +130,15 @@ class Context:
         self.check(self._L.qz_ctx_get_timing(self.handle, C.byref(ms), C.byref(n)))
         return ms.value, int(n.value)
 
+    def set_scan_chaining(self, enabled=True):
+        """promise that nothing writing a scan's inputs is enqueued between consecutive *_dev scans on this context's
+        (caller-provided) stream, so that they may overlap at the edges (include/qz_cuda.h)"""
+        self.check(self._L.qz_ctx_set_scan_chaining(self.handle, int(bool(enabled))))
+
+    def set_phase_stamps(self, d_ptr):
+        """device buffer of sm_count x 8 u64 the scan kernels write their phase stamps to (0 / None = off)"""
+        self.check(self._L.qz_ctx_set_phase_stamps(self.handle, C.c_void_p(int(d_ptr) if d_ptr else None)))
+
     @property
     def stream_handle(self):
         """the cudaStream_t (as an int) the context's `*_dev` calls enqueue on"""

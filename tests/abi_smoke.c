@@ -16,7 +16,7 @@ static const struct {
     fn f;
 } table[] = {
     F(qz_ctx_create), F(qz_ctx_destroy), F(qz_last_error), F(qz_last_global_error), F(qz_ctx_synchronize),
-    F(qz_ctx_stream), F(qz_ctx_launch_count), F(qz_ctx_sm_count), F(qz_ctx_set_timing), F(qz_ctx_get_timing),
+    F(qz_ctx_stream), F(qz_ctx_launch_count), F(qz_ctx_sm_count), F(qz_ctx_set_timing), F(qz_ctx_get_timing), F(qz_ctx_set_phase_stamps), F(qz_ctx_set_scan_chaining),
     F(qz_u8_actual_dim), F(qz_u8_row_bytes), F(qz_u8_index_create), F(qz_u8_index_set_params), F(qz_u8_encode),
     F(qz_u8_encode_dev), F(qz_u8_minmax_dev), F(qz_u8_quantile_dev), F(qz_u8_encode_range_dev), F(qz_u8_search_batch),
     F(qz_u8_search_batch_dev), F(qz_merge_topk_batch_dev), F(qz_bin_row_bytes), F(qz_bin_index_create), F(qz_bin_encode),
