@@ -47,6 +47,7 @@ struct qz_ctx {
     // (qz_ctx_set_scan_chaining), and no other kernel of this library was launched in between.
     bool chain_ok = false;      // caller's promise for a stream the context does not own
     uint64_t chain_tail = 0;    // value of `launches` right after the last chainable scan launch, 0 = none
+    uint64_t scan_seq = 0;      // fused scans launched with a tile counter (picks one of the two counters)
     bool pdl_next = false;      // launch_one: give the next launch the programmatic-serialization attribute
     uint64_t *d_stamps = nullptr;  // qz_ctx_set_phase_stamps: [sm_count][QZ_STAMP_WORDS], or NULL
     uint64_t timed_n = 0;

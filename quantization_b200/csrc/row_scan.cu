@@ -42,7 +42,7 @@ static bool plan_row_scan(const qz_ctx *ctx, uint64_t count, uint32_t row_bytes,
     const uint64_t want_tiles = 2ull * ctx->sm_count;
     while (tile_rows > align && (count + tile_rows - 1) / tile_rows < want_tiles) tile_rows -= align;
     uint32_t slot_bytes = (tile_rows * row_bytes + 127) / 128 * 128;
-    const size_t fixed = (size_t)Kp * 8 + (size_t)kConsumerWarps * kCandPerWarp * 8 + 2 * kMaxSlots * 8 + 16;
+    const size_t fixed = (size_t)Kp * 8 + (size_t)kConsumerWarps * kCandPerWarp * 8 + 2 * kMaxSlots * 8 + 16 + kMaxSlots * 4;
     if (ctx->smem_optin < fixed + (size_t)slot_bytes) return false;
     uint32_t fit = (uint32_t)((ctx->smem_optin - fixed) / slot_bytes);
     uint32_t n_slots = 1;
@@ -159,6 +159,17 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
             m.ids = fin->d_ids;
             p.done = ctx->d_done;
             *fin->fused = true;
+            // tile counter (row_scan.cuh): one CTA per SM and a static part of at least the top-k warm-up and half of
+            // a CTA's share.  Two counters alternate: a chained scan starts while its predecessor's last CTA is still
+            // merging, but never before the scan before that one has completed (with one CTA per SM the predecessor
+            // cannot be fully resident, hence cannot let ITS dependents go, until then).
+            const uint32_t share = pl.n_tiles / grid;
+            const uint32_t warm_tiles = Kp == (uint32_t)kCandPerWarp ? scan_warm_rounds(p.warm_rows, p.n_groups, p.tile_rows) * p.n_groups : 0;
+            const uint32_t n_static = warm_tiles > share / 2 ? warm_tiles : share / 2;
+            if (grid == (uint32_t)ctx->sm_count && share >= 8 && n_static <= share && !tune_flag("QZ_SCAN_STATIC_TILES")) {
+                p.n_static = n_static;
+                p.tile_ctr = ctx->d_done + 16 + 16 * (ctx->scan_seq++ & 1);
+            }
             if (fin->px) {
                 p.px = *static_cast<const PeerExchange *>(fin->px);
                 m.keys = p.px.gather[p.px.rank] + ((size_t)p.px.buf * p.px.world + p.px.rank) * kPeerStride;

@@ -66,7 +66,24 @@ struct RowScanParams {
     MergeParams merge;
     PeerExchange px;  // px.world > 1: merge.keys points at this GPU's own gather slot; see PeerExchange
     uint64_t *stamps;  // optional [gridDim.x][QZ_STAMP_WORDS] phase stamps (qz_ctx_set_phase_stamps)
+    // Tile schedule.  Local tile t of a CTA is global tile blockIdx.x + t * gridDim.x while t < n_static; later
+    // tiles are drawn from a device-wide counter (global tile gridDim.x * n_static + ticket), a few at a time,
+    // so a CTA that starts late (the SM was still merging the previous scan of a chain) or runs on a slower SM simply
+    // takes fewer of them.  tile_ctr == NULL: every tile is static (n_static is ignored).
+    uint32_t n_static;
+    uint32_t *tile_ctr;  // zero before the launch; the last CTA leaves it zero again
 };
+constexpr uint32_t kTileChunk = 32;  // largest draw from the tile counter
+constexpr uint32_t kNoTile = 0xFFFFFFFFu;
+
+// tiles of a CTA that go through the top-k warm-up (0: no warm-up); shared by the kernel and the host's planning
+__host__ __device__ __forceinline__ uint32_t scan_warm_rounds(uint32_t warm_rows, uint32_t n_groups, uint32_t tile_rows) {
+    const uint32_t cap = (uint32_t)(kConsumerWarps * kCandPerWarp), per_round = n_groups * tile_rows;
+    if (per_round > cap) return 0;
+    uint32_t r = (warm_rows + per_round - 1) / per_round;
+    if (r * per_round > cap) r = cap / per_round;
+    return r;
+}
 
 __device__ __forceinline__ uint64_t global_ns() {
     uint64_t t;
@@ -97,6 +114,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     uint64_t *empty = full + kMaxSlots;
     uint64_t *thr = empty + kMaxSlots;
     int *lock = reinterpret_cast<int *>(thr + 1);
+    uint32_t *slot_tile = reinterpret_cast<uint32_t *>(thr + 2);  // [kMaxSlots] global tile held by each slot
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool do_topk = p.partial != nullptr;
@@ -132,19 +150,47 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
         if (lane == 0) {
             const uint64_t pol = l2_policy_evict_first();
             uint32_t slot = 0, round = 0;
-            uint64_t off = (uint64_t)blockIdx.x * tile_bytes;
-            const uint64_t step = (uint64_t)gridDim.x * tile_bytes;
-            for (uint32_t t = 0; t < my_tiles; t++, off += step) {
+            // global tile gt (or kNoTile: this CTA's stream ends here for the group that owns the slot) -> next slot
+            auto issue = [&](uint32_t gt) {
                 if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
-                uint64_t bytes = p.total_bytes16 - off;
-                if (bytes > tile_bytes) bytes = tile_bytes;
-                mbar_arrive_expect_tx(&full[slot], (uint32_t)bytes);
-                bulk_g2s_hint(ring + (size_t)slot * p.slot_bytes, p.storage + off, (uint32_t)bytes, &full[slot], pol);
+                slot_tile[slot] = gt;
+                if (gt != kNoTile) {
+                    const uint64_t off = (uint64_t)gt * tile_bytes;
+                    uint64_t bytes = p.total_bytes16 - off;
+                    if (bytes > tile_bytes) bytes = tile_bytes;
+                    mbar_arrive_expect_tx(&full[slot], (uint32_t)bytes);
+                    bulk_g2s_hint(ring + (size_t)slot * p.slot_bytes, p.storage + off, (uint32_t)bytes, &full[slot], pol);
+                } else {
+                    mbar_arrive(&full[slot]);
+                }
                 if (++slot == n_slots) {
                     slot = 0;
                     round++;
                 }
+            };
+            if (p.tile_ctr) {
+                // guided self-scheduling: a draw takes 1 / (2 * CTAs) of what is left (at most kTileChunk tiles, at
+                // least one), so the counter sees a few dozen atomics per CTA and the last draws are single tiles;
+                // the next draw is always in flight while the current one is issued
+                const uint32_t base = gridDim.x * p.n_static, n_dyn = p.n_tiles - base;
+                auto want = [&](uint32_t drawn) {
+                    const uint32_t sz = (drawn < n_dyn ? n_dyn - drawn : 0) / (2 * gridDim.x);
+                    return sz < 1 ? 1u : (sz > kTileChunk ? kTileChunk : sz);
+                };
+                uint32_t sz_next = want(0);
+                uint32_t c_next = atomicAdd(p.tile_ctr, sz_next);  // in flight during the static part
+                for (uint32_t t = 0; t < p.n_static; t++) issue(blockIdx.x + t * gridDim.x);
+                for (;;) {
+                    const uint32_t c = c_next, sz = sz_next;
+                    if (c >= n_dyn) break;
+                    sz_next = want(c + sz);
+                    c_next = atomicAdd(p.tile_ctr, sz_next);
+                    for (uint32_t j = 0; j < sz && c + j < n_dyn; j++) issue(base + c + j);
+                }
+            } else {
+                for (uint32_t gt = blockIdx.x; gt < p.n_tiles; gt += gridDim.x) issue(gt);
             }
+            for (uint32_t g = 0; g < n_groups; g++) issue(kNoTile);  // every group finds one at its next local tile
         }
         return;
     }
@@ -192,21 +238,16 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     // fills its 128-entry buffer within 16 steps and the 16 lock-serialised flushes that follow
     // stall the whole ring (measured: +80 us on a 218 us scan).
     const bool coop = do_topk && p.Kp == (uint32_t)kCandPerWarp;
-    uint32_t warm_rounds = 0;
-    if (coop && n_groups * p.tile_rows <= (uint32_t)(kConsumerWarps * kCandPerWarp)) {
-        const uint32_t per_round = n_groups * p.tile_rows;
-        warm_rounds = (p.warm_rows + per_round - 1) / per_round;
-        if (warm_rounds * per_round > (uint32_t)(kConsumerWarps * kCandPerWarp))
-            warm_rounds = (kConsumerWarps * kCandPerWarp) / per_round;
-    }
+    const uint32_t warm_rounds = coop ? scan_warm_rounds(p.warm_rows, n_groups, p.tile_rows) : 0;
 
     uint32_t round = 0;
-    bool warm = warm_rounds > 0;
+    bool warm = warm_rounds > 0, ended = false;
     for (uint32_t t = group;; t += n_groups, round++) {
         if (warm && round == warm_rounds) {
             // ---- end of warm-up: cooperative reduction of the staged keys (all consumer warps) ----
+            // (with a tile counter the host makes the static part at least the warm-up, and every CTA has all of it)
             uint32_t tiles_w = warm_rounds * n_groups;
-            if (tiles_w > my_tiles) tiles_w = my_tiles;
+            if (!p.tile_ctr && tiles_w > my_tiles) tiles_w = my_tiles;
             const uint32_t n_keys = tiles_w * p.tile_rows;
             const uint32_t n_chunks = (n_keys + kCandPerWarp - 1) / kCandPerWarp;
             named_bar_sync(1, kConsumerWarps * 32);
@@ -220,14 +261,20 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             stamp(p, 2, threadIdx.x == 0);
             warm = false;
         }
-        if (t >= my_tiles) {
+        if (ended) {
             if (warm) continue;  // (fewer tiles than warm-up rounds: keep counting rounds up to the barrier)
             break;
         }
         const uint32_t slot = t & slot_mask;
         const uint32_t *sl = reinterpret_cast<const uint32_t *>(ring + (size_t)slot * p.slot_bytes);
         mbar_wait(&full[slot], (t >> slot_shift) & 1);
-        const uint32_t row0 = (blockIdx.x + t * gridDim.x) * p.tile_rows;
+        const uint32_t gt = slot_tile[slot];
+        if (gt == kNoTile) {
+            ended = true;
+            if (warm) continue;
+            break;
+        }
+        const uint32_t row0 = gt * p.tile_rows;
         const uint32_t left = p.count - row0;
         const uint32_t rows_valid = left < p.tile_rows ? left : p.tile_rows;
         const uint32_t rows_iter = warm ? p.tile_rows : rows_valid;  // warm-up also writes the empty keys of missing rows
@@ -389,7 +436,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             named_bar_sync(1, kConsumerWarps * 32);
             if (is_last) {
                 prune_merge<1, true>(p.merge, reinterpret_cast<uint64_t *>(ring), threadIdx.x, kConsumerWarps * 32);
-                if (threadIdx.x == 0) *p.done = 0;
+                if (threadIdx.x == 0) {
+                    *p.done = 0;
+                    if (p.tile_ctr) *p.tile_ctr = 0;
+                }
                 stamp(p, 5, threadIdx.x == 0);
                 if (p.px.world > 1) peer_exchange_merge(p.px, p.k, reinterpret_cast<uint64_t *>(ring));
                 stamp(p, 6, threadIdx.x == 0);
