@@ -61,6 +61,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="rows of the CPU baseline (default: the full shard)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-others", action="store_true", help="skip the other_workloads entries of the default run")
+    ap.add_argument("--no-chain", action="store_true", help="ordinary launches instead of chained scans (qz_ctx_set_scan_chaining)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl", "gather"],
                     help="N > 1: top-k exchange inside the scan launch over peer memory (all ranks get the result), "
                          "NCCL all-gather + merge launch, or the rooted peer-memory gather (rank 0 gets the result)")
@@ -326,6 +327,9 @@ def run_gpu(args):
     stream = torch.cuda.Stream(device=dev)  # a real (non-default) stream shared by torch, NCCL and libqz_cuda
     torch.cuda.set_stream(stream)
     ctx = qz.Context(local, stream=stream.cuda_stream)
+    # back-to-back device-resident scans are chained (programmatic dependent launch): nothing else is enqueued on this
+    # stream between two steps of the timed loop, which is the promise qz_ctx_set_scan_chaining asks for
+    ctx.set_scan_chaining(not args.no_chain)
     T = Timed(torch, dist, stream, world, ctx)
     q_host = host_query(wl)
     mode = args.exchange if world > 1 else "none"
@@ -348,6 +352,11 @@ def run_gpu(args):
 
         ms = T.run(step_dev, steps, warmup)
         out["launches"] = T.launches
+        # the same loop with ordinary (fully serialised) launches, for the record
+        ctx.set_scan_chaining(False)
+        plain_steps = max(steps // 4, 20)
+        out["plain_ms_per_step"] = T.max_over_ranks([T.run(step_dev, plain_steps, 3) / plain_steps], dev)[0]
+        ctx.set_scan_chaining(not args.no_chain)
         # the dominant kernel alone: the same loop again with in-stream events around each scan launch.  (A second,
         # event-bracketed pass: its per-launch mean can differ from ms_per_step by a percent either way.)
         ctx.set_timing(True)
@@ -417,6 +426,7 @@ def run_gpu(args):
                   "efficiency_vs_n1": t1 / (world * tn),
                   "e2e": {"value": rows * args.steps / (sm["e2e_ms"] * 1e-3), "ms_per_step": sm["e2e_ms"] / args.steps},
                   "kernel_ms": sm["kern_ms"] / max(sm["kern_n"], 1),
+                  "ms_per_step_unchained": sm["plain_ms_per_step"],
                   "global_topk_matches_merge_of_shards": sm.get("global_ok"),
                   "note": f"the BASELINE corpus split over {world} GPUs: {(hi - lo) * wl['row_bytes'] / 1e6:.0f} MB per GPU "
                           f"= {(hi - lo) * wl['row_bytes'] / 6.5e6:.0f} us of HBM time per step against a fixed cost "
@@ -446,6 +456,11 @@ def run_gpu(args):
                                    "peer": "peer memory inside the scan launch (qz_scan_topk_peer_dev): every rank ends with the global top-k",
                                    "gather": "peer memory inside the scan launch, rooted (qz_scan_topk_gather_dev): rank 0 ends with the global top-k",
                                    "nccl": "NCCL all-gather of k keys + merge launch"}[mode],
+                      "launches": ("chained: consecutive scans are launched as programmatic dependents, so the final "
+                                   "cross-CTA merge (and exchange) of step i overlaps the streaming of step i+1; every step "
+                                   "still scans the whole shard and produces its own top-k" if not args.no_chain else
+                                   "ordinary stream-ordered launches (--no-chain)"),
+                      "ms_per_step_unchained": weak["plain_ms_per_step"],
                       "l2": f"input {rows * wl['row_bytes'] / 1e6:.0f} MB per GPU per step "
                             + ("exceeds" if rows * wl["row_bytes"] > 126e6 else "FITS IN") + " the 126 MB L2; no flush"},
             "e2e": {"value": total_rows * args.steps / (e2e_ms * 1e-3), "unit": "vectors/s",

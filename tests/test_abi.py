@@ -3,6 +3,7 @@ No compute here (no GPU on the CPU box)."""
 import ctypes
 import os
 import re
+import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -69,3 +70,13 @@ def test_no_gpu_fails_loudly():
     import quantization_b200 as qz
     with pytest.raises(qz.EncodingError):
         qz.Context(0)
+
+
+def test_rust_ffi_declarations_are_current():
+    """rust/cuda_ffi.rs is generated from include/qz_cuda.h (tools/gen_rust_ffi.py) and must declare every symbol"""
+    import subprocess
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_rust_ffi.py"), "--check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    rs = open(os.path.join(ROOT, "rust", "cuda_ffi.rs")).read()
+    for sym in header_symbols():
+        assert f"pub fn {sym}(" in rs, sym
