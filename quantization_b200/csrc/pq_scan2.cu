@@ -86,18 +86,24 @@ __device__ __forceinline__ float pq2_gather(uint32_t cw, uint32_t lane_const, ui
 // lc0 = the lane constant of pq2_gather for j = 0; step j uses lc0 ^ 4j.  Returns the row's slice sum.
 template <bool FAST>
 __device__ __forceinline__ float pq2_rows16(const uint32_t (&cw)[16], uint32_t lc0, uint32_t lut_s) {
-    float s0, s1, s2, s3;
+    // The words arrive in the order w = (L & 15) ^ j, which depends on the row's position.  The sum must not: a row
+    // scores the same wherever it sits (a shard of the corpus and the whole corpus agree bit for bit).  A balanced
+    // tree over j that pairs j with j ^ 1, then ^ 2, ^ 4, ^ 8 pairs the same WORDS whatever the xor mask, and a + b
+    // is commutative, so its value is that of the same tree over w.
+    float w[16];
 #pragma unroll
     for (int j = 0; j < 16; j++) {
         const uint32_t lc = lc0 ^ (4u * j);
         const float g0 = pq2_gather<FAST, 0>(cw[j], lc, lut_s), g1 = pq2_gather<FAST, 1>(cw[j], lc, lut_s);
         const float g2 = pq2_gather<FAST, 2>(cw[j], lc, lut_s), g3 = pq2_gather<FAST, 3>(cw[j], lc, lut_s);
-        s0 = j ? __fadd_rn(s0, g0) : g0;
-        s1 = j ? __fadd_rn(s1, g1) : g1;
-        s2 = j ? __fadd_rn(s2, g2) : g2;
-        s3 = j ? __fadd_rn(s3, g3) : g3;
+        w[j] = __fadd_rn(__fadd_rn(g0, g1), __fadd_rn(g2, g3));
     }
-    const float s = __fadd_rn(__fadd_rn(s0, s2), __fadd_rn(s1, s3));
+#pragma unroll
+    for (int d = 1; d < 16; d <<= 1) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 2 * d) w[j] = __fadd_rn(w[j], w[j + d]);
+    }
+    const float s = w[0];
     return __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, 16));
 }
 

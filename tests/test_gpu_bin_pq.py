@@ -165,6 +165,29 @@ def test_pq_streaming_scan_blocks(ctx, dim, chunk, count):
             assert np.array_equal(k_i, e_i) and np.array_equal(bits(k_s), bits(e_s))
 
 
+def test_pq_scan_score_does_not_depend_on_row_position(ctx):
+    """a shard of a corpus and the whole corpus must agree bit for bit (tools/peer_check.py): the scan
+    sums a row's lookups in an order that is the same wherever the row sits (any offset mod 16 / 64, any CTA)"""
+    dim, chunk, count = 512, 2, 40_000
+    n_chunks = dim // chunk
+    rng = np.random.default_rng(11)
+    codes = rng.integers(0, 256, size=(count, n_chunks), dtype=np.uint8)
+    cen = O.uniform(7, 256 * dim).reshape(256, dim)
+    query = O.uniform(8, dim)
+    whole = qz.EncodedVectorsPQ(ctx, codes.reshape(-1), qz.VectorParameters(dim, count, qz.DistanceType.Dot, False), chunk, cen)
+    lut = whole.encode_query(query)
+    ref = whole.score_all(lut)
+    for lo, hi in ((1, count), (13, 30_001), (20_003, count), (64, 128)):
+        part = qz.EncodedVectorsPQ(ctx, codes[lo:hi].reshape(-1), qz.VectorParameters(dim, hi - lo, qz.DistanceType.Dot, False),
+                                   chunk, cen, id_base=lo)
+        assert np.array_equal(bits(part.score_all(lut)), bits(ref[lo:hi])), (lo, hi)
+        s, i = part.search_top_k(lut, 50, True)
+        es, ei = O.topk(ref[lo:hi], 50, True, id_base=lo)
+        assert np.array_equal(i, ei) and np.array_equal(bits(s), bits(es))
+        part.close()
+    whole.close()
+
+
 def test_pq_kmeans_training(ctx):
     """real k-means on the device (count > 256): reference tolerance + quantization error no worse than
     the CPU oracle's k-means by more than 2%"""
