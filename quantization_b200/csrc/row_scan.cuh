@@ -394,20 +394,58 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
         __syncwarp();
         stamp(p, 3, threadIdx.x == 0);
         if (coop) {
-            // every warp pads its leftovers to a full chunk; the 16 chunks are reduced together
-            for (int i = cnt + lane; i < kCandPerWarp; i += 32) cand[i] = 0ull;
+            // Leftovers.  Most of what is still staged no longer beats the CTA's k-th best: every warp first drops
+            // those keys and packs the rest into one shared chunk.  Usually they all fit one chunk, which one warp
+            // sorts and merges into the list (2 barriers); otherwise every warp pads what it kept to a full chunk and
+            // the 16 chunks are reduced together as before.
+            const uint64_t th = *thr;
+            int kept = 0;
+            for (int base = 0; base < cnt; base += 32) {
+                const uint64_t c = base + (int)lane < cnt ? cand[base + lane] : 0ull;
+                const bool keep = c > th;
+                const uint32_t mk = __ballot_sync(0xffffffffu, keep);
+                __syncwarp();
+                if (keep) cand[kept + __popc(mk & ((1u << lane) - 1))] = c;
+                kept += __popc(mk);
+                __syncwarp();
+            }
+            cnt = kept;
+            uint32_t *n_left = reinterpret_cast<uint32_t *>(lock);  // the flush lock is idle from here on
+            named_bar_sync(1, kConsumerWarps * 32);                 // (all flushes done, `lock` is 0)
+            uint32_t pos0 = 0;
+            if (lane == 0 && cnt) pos0 = atomicAdd(n_left, (uint32_t)cnt);
+            pos0 = __shfl_sync(0xffffffffu, pos0, 0);
             named_bar_sync(1, kConsumerWarps * 32);
-            coop_top128(cand_all, kConsumerWarps * kCandPerWarp, kConsumerWarps, warp, lane);
-            if (warp == 0) {
-                uint64_t t4[4];
+            const uint32_t total = *n_left;
+            if (total <= (uint32_t)kCandPerWarp) {
+                // the shared chunk is warp 0's staging area, which may hold warp 0's own leftovers: everybody reads
+                // its keys into registers, then (barrier) writes them to their place
+                uint64_t mine[4];
 #pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    const uint64_t a = top[lane * 4 + r], b = cand_all[kCandPerWarp - 1 - (lane * 4 + r)];
-                    t4[r] = a > b ? a : b;
+                for (int r = 0; r < 4; r++) mine[r] = (int)(lane + 32 * r) < cnt ? cand[lane + 32 * r] : 0ull;
+                named_bar_sync(1, kConsumerWarps * 32);  // (and everyone has read `total`)
+                if (threadIdx.x == 0) *n_left = 0;       // it is the flush lock again
+#pragma unroll
+                for (int r = 0; r < 4; r++)
+                    if ((int)(lane + 32 * r) < cnt) cand_all[pos0 + lane + 32 * r] = mine[r];
+                named_bar_sync(1, kConsumerWarps * 32);
+                if (warp == 0 && total) cta_topk_flush(st, cand_all, (int)total, lane);
+            } else {
+                for (int i = cnt + lane; i < kCandPerWarp; i += 32) cand[i] = 0ull;
+                named_bar_sync(1, kConsumerWarps * 32);  // (and everyone has read `total`)
+                if (threadIdx.x == 0) *n_left = 0;
+                coop_top128(cand_all, kConsumerWarps * kCandPerWarp, kConsumerWarps, warp, lane);
+                if (warp == 0) {
+                    uint64_t t4[4];
+#pragma unroll
+                    for (int r = 0; r < 4; r++) {
+                        const uint64_t a = top[lane * 4 + r], b = cand_all[kCandPerWarp - 1 - (lane * 4 + r)];
+                        t4[r] = a > b ? a : b;
+                    }
+                    reg128_merge_desc(t4, lane);
+#pragma unroll
+                    for (int r = 0; r < 4; r++) top[lane * 4 + r] = t4[r];
                 }
-                reg128_merge_desc(t4, lane);
-#pragma unroll
-                for (int r = 0; r < 4; r++) top[lane * 4 + r] = t4[r];
             }
         } else if (cnt > 0) {
             cta_topk_flush(st, cand, cnt, lane);
