@@ -85,7 +85,7 @@ __device__ __forceinline__ void peer_exchange_merge(const PeerExchange &x, uint3
             }
         }
         named_bar_sync(1, T);
-        prune_merge<1, true>(x.merge, work, threadIdx.x, T);
+        few_lists_merge<1, true>(x.merge, work, threadIdx.x, T);  // world <= kMaxPeers lists of k <= 128 keys
         named_bar_sync(1, T);  // every list has been read: the peers may overwrite this buffer half
         peer_send_acks(x);
         return;
@@ -110,7 +110,7 @@ __device__ __forceinline__ void peer_exchange_merge(const PeerExchange &x, uint3
         }
     }
     named_bar_sync(1, T);
-    prune_merge<1, true>(x.merge, work, threadIdx.x, T);
+    few_lists_merge<1, true>(x.merge, work, threadIdx.x, T);  // world <= kMaxPeers lists of k <= 128 keys
     named_bar_sync(1, T);
     peer_send_acks(x);
 }

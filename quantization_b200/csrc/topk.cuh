@@ -495,6 +495,37 @@ __device__ __forceinline__ void prune_merge(const MergeParams &p, uint64_t *s, u
     write_final(p, s, P, tid, T);
 }
 
+// Final merge of a FEW sorted lists (the world's lists after the cross-GPU exchange: G <= 16, at most 128 keys each):
+// list g becomes chunk g of the work area, then a pairwise max-merge tree in registers, one warp per pair, log2(G)
+// levels.  About a third of prune_merge's latency at G = 8 (no probes, no ranking, no sort).  T = 512 threads.
+template <int BAR, bool CG>
+__device__ __forceinline__ void few_lists_merge(const MergeParams &p, uint64_t *s, uint32_t tid, uint32_t T) {
+    const uint32_t G = p.n_lists, lane = tid & 31, warp = tid >> 5;
+    uint32_t Gp = 1;
+    while (Gp < G) Gp <<= 1;
+    for (uint32_t i = tid; i < Gp * 128; i += T) {
+        const uint32_t g = i >> 7, j = i & 127;
+        s[i] = (g < G && j < p.in_len) ? ld_list<CG>(p.in + (size_t)g * p.in_stride + j) : 0ull;
+    }
+    grp_sync<BAR>(T);
+    for (uint32_t stride = 1; stride < G; stride <<= 1) {
+        if ((warp & (2 * stride - 1)) == 0 && warp + stride < G) {
+            uint64_t *A = s + warp * 128, *B = s + (warp + stride) * 128;
+            uint64_t t[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const uint64_t a = A[lane * 4 + r], b = B[127 - (lane * 4 + r)];
+                t[r] = a > b ? a : b;
+            }
+            reg128_merge_desc(t, (int)lane);
+#pragma unroll
+            for (int r = 0; r < 4; r++) A[lane * 4 + r] = t[r];
+        }
+        grp_sync<BAR>(T);
+    }
+    write_final(p, s, 128, tid, T);
+}
+
 template <int kUnused = 0>
 __global__ void __launch_bounds__(1024, 1) prune_merge_kernel(MergeParams p) {
     extern __shared__ __align__(16) uint64_t s[];  // max(kPruneSmem, tree-merge need)

@@ -4,16 +4,18 @@
 # tools/peer_check.py at world N.  Lines are appended to gpurun_out/r2_strong_<wl>.jsonl.
 n=${1:-8}
 port=$((29800 + n))
-run() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port "$@"; port=$((port + 1)); }
+DRY=${DRY:-}
 for wl in u8 bin; do
   for ex in peer gather; do
     if [ "$n" = 1 ]; then
       [ "$ex" = gather ] && continue
-      timeout 300 python bench.py --workload $wl --no-cpu --no-others --steps 1000 > gpurun_out/tmp_line.json 2> gpurun_out/scale_r2_${wl}_${ex}_n$n.err
+      cmd="python bench.py --workload $wl --no-cpu --no-others --steps 1000"
     else
-      timeout 400 bash -c "$(declare -f run); port=$port; run bench.py --gpus $n --workload $wl --exchange $ex --no-cpu --no-others --steps 1000" > gpurun_out/tmp_line.json 2> gpurun_out/scale_r2_${wl}_${ex}_n$n.err
+      cmd="python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port bench.py --gpus $n --workload $wl --exchange $ex --no-cpu --no-others --steps 1000"
       port=$((port + 1))
     fi
+    if [ -n "$DRY" ]; then echo "$cmd"; continue; fi
+    timeout 400 $cmd > gpurun_out/tmp_line.json 2> gpurun_out/scale_r2_${wl}_${ex}_n$n.err
     tail -1 gpurun_out/tmp_line.json >> gpurun_out/r2_strong_${wl}.jsonl
     tail -1 gpurun_out/tmp_line.json | python -c "
 import json,sys
@@ -24,7 +26,10 @@ except Exception as e: print('$wl $ex FAILED', e)"
   done
 done
 if [ "$n" != 1 ]; then
-  timeout 300 bash -c "$(declare -f run); port=$((port + 7)); run tools/peer_check.py" > gpurun_out/r2_peer_check_n$n.txt 2>&1
-  grep -E "PEER_CHECK|us/step|MISMATCH" gpurun_out/r2_peer_check_n$n.txt | tail -14
+  cmd="python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((port + 7)) tools/peer_check.py"
+  if [ -n "$DRY" ]; then echo "$cmd"; else
+    timeout 300 $cmd > gpurun_out/r2_peer_check_n$n.txt 2>&1
+    grep -E "PEER_CHECK|us/step|MISMATCH" gpurun_out/r2_peer_check_n$n.txt | tail -14
+  fi
 fi
 rm -f gpurun_out/tmp_line.json
