@@ -394,10 +394,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
         __syncwarp();
         stamp(p, 3, threadIdx.x == 0);
         if (coop) {
-            // Leftovers.  Most of what is still staged no longer beats the CTA's k-th best: every warp first drops
-            // those keys and packs the rest into one shared chunk.  Usually they all fit one chunk, which one warp
-            // sorts and merges into the list (2 barriers); otherwise every warp pads what it kept to a full chunk and
-            // the 16 chunks are reduced together as before.
+            // Leftovers.  Much of what is still staged no longer beats the CTA's k-th best: every warp first drops
+            // those keys, then all warps pack the rest contiguously.  One chunk (<= 128 keys): one warp sorts and
+            // merges it into the list.  More: only the occupied chunks go through the cooperative reduction (the first
+            // version always reduced 16 padded chunks: 4 merge levels, 8 us).
             const uint64_t th = *thr;
             int kept = 0;
             for (int base = 0; base < cnt; base += 32) {
@@ -417,9 +417,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
             pos0 = __shfl_sync(0xffffffffu, pos0, 0);
             named_bar_sync(1, kConsumerWarps * 32);
             const uint32_t total = *n_left;
-            if (total <= (uint32_t)kCandPerWarp) {
-                // the shared chunk is warp 0's staging area, which may hold warp 0's own leftovers: everybody reads
-                // its keys into registers, then (barrier) writes them to their place
+            {
+                // the packed keys start in warp 0's staging area, which may still hold leftovers of its owner (and so
+                // on): everybody reads its keys into registers, then (barrier) writes them to their place
                 uint64_t mine[4];
 #pragma unroll
                 for (int r = 0; r < 4; r++) mine[r] = (int)(lane + 32 * r) < cnt ? cand[lane + 32 * r] : 0ull;
@@ -429,22 +429,22 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
                 for (int r = 0; r < 4; r++)
                     if ((int)(lane + 32 * r) < cnt) cand_all[pos0 + lane + 32 * r] = mine[r];
                 named_bar_sync(1, kConsumerWarps * 32);
-                if (warp == 0 && total) cta_topk_flush(st, cand_all, (int)total, lane);
-            } else {
-                for (int i = cnt + lane; i < kCandPerWarp; i += 32) cand[i] = 0ull;
-                named_bar_sync(1, kConsumerWarps * 32);  // (and everyone has read `total`)
-                if (threadIdx.x == 0) *n_left = 0;
-                coop_top128(cand_all, kConsumerWarps * kCandPerWarp, kConsumerWarps, warp, lane);
-                if (warp == 0) {
-                    uint64_t t4[4];
+                if (total <= (uint32_t)kCandPerWarp) {
+                    if (warp == 0 && total) cta_topk_flush(st, cand_all, (int)total, lane);
+                } else {
+                    // a few chunks: sorted in parallel, max-merge tree of log2(chunks) levels, then into the list
+                    coop_top128(cand_all, total, (total + kCandPerWarp - 1) / kCandPerWarp, warp, lane);
+                    if (warp == 0) {
+                        uint64_t t4[4];
 #pragma unroll
-                    for (int r = 0; r < 4; r++) {
-                        const uint64_t a = top[lane * 4 + r], b = cand_all[kCandPerWarp - 1 - (lane * 4 + r)];
-                        t4[r] = a > b ? a : b;
+                        for (int r = 0; r < 4; r++) {
+                            const uint64_t a = top[lane * 4 + r], b = cand_all[kCandPerWarp - 1 - (lane * 4 + r)];
+                            t4[r] = a > b ? a : b;
+                        }
+                        reg128_merge_desc(t4, lane);
+#pragma unroll
+                        for (int r = 0; r < 4; r++) top[lane * 4 + r] = t4[r];
                     }
-                    reg128_merge_desc(t4, lane);
-#pragma unroll
-                    for (int r = 0; r < 4; r++) top[lane * 4 + r] = t4[r];
                 }
             }
         } else if (cnt > 0) {

@@ -16,7 +16,7 @@ for wl in u8 bin; do
     fi
     if [ -n "$DRY" ]; then echo "$cmd"; continue; fi
     timeout 400 $cmd > gpurun_out/tmp_line.json 2> gpurun_out/scale_r2_${wl}_${ex}_n$n.err
-    tail -1 gpurun_out/tmp_line.json >> gpurun_out/r2_strong_${wl}.jsonl
+    tail -1 gpurun_out/tmp_line.json >> gpurun_out/r2_strong_${wl}_n${n}.jsonl
     tail -1 gpurun_out/tmp_line.json | python -c "
 import json,sys
 try:
