@@ -159,14 +159,14 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
             m.ids = fin->d_ids;
             p.done = ctx->d_done;
             *fin->fused = true;
-            // tile counter (row_scan.cuh): one CTA per SM and a static part of at least the top-k warm-up and half of
-            // a CTA's share.  Two counters alternate: a chained scan starts while its predecessor's last CTA is still
-            // merging, but never before the scan before that one has completed (with one CTA per SM the predecessor
-            // cannot be fully resident, hence cannot let ITS dependents go, until then).
+            // tile counter (row_scan.cuh): one CTA per SM; the static part is one ring of tiles, everything else is drawn,
+            // so a CTA that starts late (its SM was still merging and exchanging the previous scan of a chain: 10-25 us)
+            // does little more than that ring.  Two counters alternate: a chained scan starts while its predecessor's
+            // last CTA is still merging, but never before the scan before that one has completed (with one CTA per SM
+            // the predecessor cannot be fully resident, hence cannot let ITS dependents go, until then).
             const uint32_t share = pl.n_tiles / grid;
-            const uint32_t warm_tiles = Kp == (uint32_t)kCandPerWarp ? scan_warm_rounds(p.warm_rows, p.n_groups, p.tile_rows) * p.n_groups : 0;
-            const uint32_t n_static = warm_tiles > share / 2 ? warm_tiles : share / 2;
-            if (grid == (uint32_t)ctx->sm_count && share >= 8 && n_static <= share && !tune_flag("QZ_SCAN_STATIC_TILES")) {
+            const uint32_t n_static = p.n_slots;
+            if (grid == (uint32_t)ctx->sm_count && share >= 2 * n_static && !tune_flag("QZ_SCAN_STATIC_TILES")) {
                 p.n_static = n_static;
                 p.tile_ctr = ctx->d_done + 16 + 16 * (ctx->scan_seq++ & 1);
             }

@@ -66,7 +66,8 @@ struct RowScanParams {
     MergeParams merge;
     PeerExchange px;  // px.world > 1: merge.keys points at this GPU's own gather slot; see PeerExchange
     uint64_t *stamps;  // optional [gridDim.x][QZ_STAMP_WORDS] phase stamps (qz_ctx_set_phase_stamps)
-    // Tile schedule.  Local tile t of a CTA is global tile blockIdx.x + t * gridDim.x while t < n_static; later
+    // Tile schedule.  Local tile t of a CTA is global tile blockIdx.x + t * gridDim.x while t < n_static (one ring's
+    // worth: they are issued while the first draw is in flight); later
     // tiles are drawn from a device-wide counter (global tile gridDim.x * n_static + ticket), a few at a time,
     // so a CTA that starts late (the SM was still merging the previous scan of a chain) or runs on a slower SM simply
     // takes fewer of them.  tile_ctr == NULL: every tile is static (n_static is ignored).
@@ -135,6 +136,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     }
     if (do_topk)
         for (uint32_t i = threadIdx.x; i < p.Kp; i += blockDim.x) top[i] = 0;
+    // with a tile counter a CTA may draw fewer tiles than the warm-up covers (it started late and the pool was empty):
+    // the warm-up's staging area starts as empty keys, and the reduction always takes all of it
+    if (do_topk && p.tile_ctr)
+        for (uint32_t i = threadIdx.x; i < (uint32_t)(kConsumerWarps * kCandPerWarp); i += blockDim.x) cand_all[i] = 0ull;
     __syncthreads();
     // A scan launched behind this one as a programmatic dependent (row_scan.cu, chained launches) may take the SMs
     // this grid's CTAs leave while the last CTA is still merging; it waits for this grid to complete before it
@@ -245,7 +250,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     for (uint32_t t = group;; t += n_groups, round++) {
         if (warm && round == warm_rounds) {
             // ---- end of warm-up: cooperative reduction of the staged keys (all consumer warps) ----
-            // (with a tile counter the host makes the static part at least the warm-up, and every CTA has all of it)
+            // (with a tile counter: all of the zero-initialised staging area, whatever this CTA got to draw)
             uint32_t tiles_w = warm_rounds * n_groups;
             if (!p.tile_ctr && tiles_w > my_tiles) tiles_w = my_tiles;
             const uint32_t n_keys = tiles_w * p.tile_rows;
