@@ -468,7 +468,8 @@ def run_gpu(args):
                     "d2h_bytes_per_step": int(2 * k * 4),  # one copy: k scores and k ids are contiguous on the device
                     "ms_per_step": e2e_ms / args.steps,
                     "call": ("qz_search_topk_peer" if use_peer else "qz_search_topk") +
-                            " (host f32 query -> host scores, ids), one call per step"},
+                            " (host f32 query -> host scores, ids), one call per step; the query is read from, and the "
+                            "results are written to, pinned host memory by the kernels themselves (no copy operations)"},
             "gpu_launches": int(weak["launches"]),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src,

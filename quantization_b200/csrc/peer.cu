@@ -180,29 +180,27 @@ static qz_status search_topk_exchange(qz_index *ix, qz_peer *pe, int32_t root, c
     const size_t fb_pad = (fb + 255) / 256 * 256, qb_pad = (qb + 255) / 256 * 256;
     QZ_TRY(ensure_query(ctx, fb_pad + qb_pad + 16));
     QZ_TRY(ensure_pin(ctx, fb_pad + (size_t)2 * QZ_MAX_K * 4));
-    uint8_t *d_f32 = ctx->d_query, *d_blob = ctx->d_query + fb_pad;
-    if (pe->staged_pending) {
+    uint8_t *d_blob = ctx->d_query + fb_pad;
+    if (pe->staged_pending) {  // a non-root call may still be reading the staged query
         QZ_CUDA(ctx, cudaEventSynchronize(pe->staged));
         pe->staged_pending = false;
     }
+    // no copy operations: the pinned staging buffer is read (f32 query) and written (k scores, k ids) by the kernels
+    // in place, as in qz_search_topk
     memcpy(ctx->h_pin, query, fb);
-    QZ_CUDA(ctx, cudaMemcpyAsync(d_f32, ctx->h_pin, fb, cudaMemcpyHostToDevice, ctx->stream));
+    QZ_TRY(qz_encode_query_dev(ix, reinterpret_cast<const float *>(ctx->h_pin), 1, d_blob));
     if (root >= 0 && pe->world > 1 && (uint32_t)root != pe->rank) {
         if (!pe->staged) QZ_CUDA(ctx, cudaEventCreateWithFlags(&pe->staged, cudaEventDisableTiming));
-        QZ_CUDA(ctx, cudaEventRecord(pe->staged, ctx->stream));
+        QZ_CUDA(ctx, cudaEventRecord(pe->staged, ctx->stream));  // (after the kernel that reads the staged query)
         pe->staged_pending = true;
     }
-    QZ_TRY(qz_encode_query_dev(ix, reinterpret_cast<const float *>(d_f32), 1, d_blob));
-    // the k ids go right behind the k scores: one copy of 2 * k * 4 bytes brings both back
-    QZ_TRY(scan_topk_exchange(ix, pe, root, d_blob, k, largest, nullptr, ctx->d_scores_k,
-                              reinterpret_cast<uint32_t *>(ctx->d_scores_k + k)));
+    float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
+    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + k);
+    QZ_TRY(scan_topk_exchange(ix, pe, root, d_blob, k, largest, nullptr, hs, hi));
     if (root >= 0 && pe->world > 1 && (uint32_t)root != pe->rank) {  // not the root: nothing comes back
         if (n_out) *n_out = 0;
         return QZ_OK;  // (asynchronous: the launch is on the stream; the caller's next call or qz_ctx_synchronize orders it)
     }
-    float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
-    uint32_t *hi = reinterpret_cast<uint32_t *>(hs + k);
-    QZ_CUDA(ctx, cudaMemcpyAsync(hs, ctx->d_scores_k, (size_t)2 * k * 4, cudaMemcpyDeviceToHost, ctx->stream));
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     uint32_t m = 0;
     while (m < k && hi[m] != 0xFFFFFFFFu) m++;  // empty slots decode to id 0xFFFFFFFF
