@@ -354,3 +354,48 @@ def test_batch_search_empty_index_and_param_update(ctx):
         ws, wi = o2.search(enc, k, True)
         assert np.array_equal(i[qi], wi) and np.array_equal(bits(s[qi]), bits(ws))
     g.close()
+
+
+# ------------------------------------------------------------------------------------------ chained scans
+def test_chained_scans_give_the_results_of_separate_scans(ctx):
+    """consecutive *_dev scans on a context that owns its stream are launched as programmatic dependents (the
+    streaming of scan i+1 overlaps the final merge of scan i, tile counters alternate): 300 back-to-back scans over
+    two indexes of different size (one CTA per SM / a few CTAs) with 8 different queries and k values, none
+    synchronised, must equal the same scans made one at a time through the host-buffer call"""
+    import torch
+    rng = np.random.default_rng(21)
+    big_n, small_n, dim = 400_000, 3_000, 256
+    big = rng.random((big_n, dim), dtype=np.float32)
+    g_big = qz.EncodedVectorsU8.encode(big, qz.VecStorageBuilder(), qz.VectorParameters(dim, big_n, qz.DistanceType.Dot, False), ctx=ctx)
+    g_small = qz.EncodedVectorsU8.encode(big[:small_n], qz.VecStorageBuilder(),
+                                         qz.VectorParameters(dim, small_n, qz.DistanceType.Dot, False), ctx=ctx)
+    b_big = qz.EncodedVectorsBin.encode(big - 0.5, qz.VecStorageBuilder(), qz.VectorParameters(dim, big_n, qz.DistanceType.Dot, False), ctx=ctx)
+    queries = [rng.random(dim, dtype=np.float32) for _ in range(8)]
+    plan = []  # (index, encoded query on the device, k, largest, expected)
+    for n in range(300):
+        ix = (g_big, g_small, b_big)[n % 3]
+        q = queries[n % 8] - (0.5 if ix is b_big else 0.0)
+        k, largest = (100, 17, 128, 1)[n % 4], n % 5 != 0
+        plan.append((ix, q, k, largest))
+    expected = {}
+    enc_dev = {}
+    for ix, q, k, largest in plan:
+        key = (id(ix), q.tobytes(), k, largest)
+        if key not in expected:
+            enc = ix.encode_query(q)
+            expected[key] = ix.search_top_k(enc, k, largest)
+            enc_dev[key] = torch.from_numpy(np.frombuffer(bytes(enc), np.uint8).copy()).cuda()
+    torch.cuda.synchronize()
+    out_s = torch.zeros((len(plan), 128), dtype=torch.float32, device="cuda")
+    out_i = torch.zeros((len(plan), 128), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    for n, (ix, q, k, largest) in enumerate(plan):  # nothing but scans on the context's stream
+        ix.search_top_k_dev(enc_dev[(id(ix), q.tobytes(), k, largest)].data_ptr(), k, largest, 0, out_s[n].data_ptr(), out_i[n].data_ptr())
+    ctx.synchronize()
+    hs, hi = out_s.cpu().numpy(), out_i.cpu().numpy().view(np.uint32)
+    for n, (ix, q, k, largest) in enumerate(plan):
+        es, ei = expected[(id(ix), q.tobytes(), k, largest)]
+        assert np.array_equal(hi[n, :ei.size], ei), n
+        assert np.array_equal(bits(hs[n, :es.size]), bits(es)), n
+    for g in (g_big, g_small, b_big):
+        g.close()
