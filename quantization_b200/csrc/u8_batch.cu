@@ -69,11 +69,24 @@ __global__ void __launch_bounds__(256) u8_vq_kernel(const float *voff, uint64_t 
 __device__ __noinline__ void queue_flush(uint32_t *cnt, uint64_t *cand, uint32_t cap, uint32_t *overflow,
                                          const uint64_t *qkeys, const uint32_t *qq, uint32_t n, uint32_t lane) {
     __syncwarp();
-    for (uint32_t e = lane; e < n; e += 32) {
-        const uint32_t q = qq[e];
-        const uint32_t pos = atomicAdd(cnt + q, 1u);
-        if (pos < cap) cand[(size_t)q * cap + pos] = qkeys[e];
-        else *overflow = 1u;
+    // all counter round trips of a flush are in flight together (the rolled loop paid them one after another: up to
+    // kQueueCap / 32 = 8 L2 atomics of ~1 us per flush, which paced the small early chunks where most of what a tile
+    // produces is a candidate)
+    constexpr int kRounds = kQueueCap / 32;
+    uint32_t q[kRounds], pos[kRounds];
+#pragma unroll
+    for (int i = 0; i < kRounds; i++) {
+        const uint32_t e = lane + 32 * i;
+        q[i] = e < n ? qq[e] : 0u;
+        pos[i] = e < n ? atomicAdd(cnt + q[i], 1u) : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < kRounds; i++) {
+        const uint32_t e = lane + 32 * i;
+        if (e < n) {
+            if (pos[i] < cap) cand[(size_t)q[i] * cap + pos[i]] = qkeys[e];
+            else *overflow = 1u;
+        }
     }
     __syncwarp();
 }
