@@ -477,7 +477,13 @@ def run_gpu(args):
                          "kernel_ms": scan_ms, "kernel_launches_timed": weak["kern_n"],
                          "kernel_ms_note": "mean of in-stream event pairs around each scan launch in a second pass of the "
                                            "same loop (not the pass ms_per_step comes from)",
-                         "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0},
+                         "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
+                         # the same ratio for the timed loop itself (chained launches: the merge of query i overlaps the
+                         # streaming of query i+1, so this is the rate of a stream of queries, not of one kernel)
+                         "stream_gbs": rows * wl["row_bytes"] / (ms / args.steps * 1e-3) / 1e9,
+                         "stream_frac": rows * wl["row_bytes"] / (ms / args.steps * 1e-3) / 1e9 / peak,
+                         "peak_note": "the peak is the driver-measured COPY bandwidth; a read-only stream can exceed it "
+                                      "(profiles/r1_hbm_probe.txt: 7.2-7.5 TB/s of bulk-copy reads)"},
             "clocks": clocks,
             "top1_id": int(weak["ids"][0]),
         }
