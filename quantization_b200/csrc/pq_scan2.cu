@@ -2,14 +2,14 @@
 //
 // score_point for every row (encoded_vectors_pq.rs:405-494): score = sum over chunks of lut[ch*256 + code[ch]].
 // The query LUT (n_chunks x 256 f32, 768 KiB at 1536-d / chunk 2) does not fit one SM's shared memory, so the
-// chunk axis is cut into slices of 128 chunks (128 KiB of LUT, bank-permuted by pq_lut_permute_kernel: lane w
-// owns code word w of the slice and all four of its gathers fall in bank w, whatever the codes).
+// chunk axis is cut into slices of 128 chunks (128 KiB of LUT, bank-permuted by pq_lut_permute_kernel: the four
+// gathers of code word w of a row-slice fall in bank w, whatever the codes; layout at pq2_gather below).
 //
 // One persistent CTA per SM owns blocks of `block_rows` consecutive rows.  For a block it walks the slices in
-// order: the slice's LUT is bulk-copied into shared memory, a producer thread streams the block's 128-byte
-// code sub-rows through a ring of 64-row tiles (2-D TMA tiles of the row-major code matrix, completing on
-// mbarriers), sixteen consumer warps gather and add, and the per-row sums accumulate in shared memory in slice
-// order.  After the last slice the block's scores are final: they are written out (4 B per row) for the top-k
+// order: the slice's LUT is bulk-copied into shared memory, four producer lanes (one per consumer group) stream
+// the block's 128-byte code sub-rows through a ring of 64-row tiles (2-D TMA tiles of the row-major code matrix,
+// completing on mbarriers), sixteen consumer warps gather and add (one row per lane, pq2_rows16), and the per-row
+// sums accumulate in shared memory in slice order.  After the last slice the block's scores are final: they are written out (4 B per row) for the top-k
 // pass, and/or (k <= 128) reduced on the spot to the CTA's running top-k list: keys above the current threshold are
 // compacted into the (idle) LUT area and reduced with the cooperative register sorting networks of topk.cuh.
 // HBM traffic = the codes, once; nothing else leaves the SM but the final scores or the k best keys.

@@ -2,8 +2,10 @@
 //
 // One persistent CTA per SM.  A producer thread streams tiles of `tile_rows` consecutive rows
 // from HBM into a shared-memory ring with 1-D bulk async copies (TMA engine, UBLKCP) that
-// complete on mbarriers; sixteen consumer warps drain it, 16 / n_slots warps per slot (a warp
-// is bound to one slot for the whole kernel, so there is no slot arithmetic in the loop).  A
+// complete on mbarriers; sixteen consumer warps in n_groups groups drain it (group g takes the CTA's local tiles
+// g, g + n_groups, ...; local tile t lives in slot t mod n_slots and n_groups divides n_slots, so a slot always
+// serves the same group).  Which GLOBAL tile a local tile is comes from a static prefix plus a device-wide tile
+// counter (RowScanParams::tile_ctr), written by the producer next to the slot's mbarrier.  A
 // warp works on 8 rows at a time: lane l owns 32-bit words l, l+32, ... of every row
 // (bank-conflict free for any row stride, and the matching query words stay in registers),
 // accumulates an exact integer per row, and a 9-shuffle butterfly leaves row r's total in a
