@@ -34,11 +34,28 @@ __global__ void __launch_bounds__(256) u8_encode_query_kernel(U8QueryParams p) {
     __syncthreads();
     const uint32_t pad = u8_code(p.distance == kDot ? 0.0f : p.offset, p.alpha, p.offset);
     unsigned long long a1 = 0, a2 = 0;
-    for (uint32_t i = threadIdx.x; i < p.actual_dim; i += blockDim.x) {
-        uint32_t c = i < p.dim ? u8_code(q[i], p.alpha, p.offset) : pad;
-        out[4 + i] = (uint8_t)c;
-        a1 += c;
-        a2 += c * c;
+    // The query may sit in pinned HOST memory (qz_search_topk passes its staging buffer): a load is then a PCIe round
+    // trip of 1-2 us, so all loads of a pass are issued before the first code is stored (a load after a byte store
+    // through `out` could not be hoisted: the two pointers may alias).  8 x 256 values per pass: one pass up to 2048-d.
+    constexpr uint32_t kInFlight = 8;
+    for (uint32_t base = 0; base < p.actual_dim; base += kInFlight * 256) {
+        float v[kInFlight];
+#pragma unroll
+        for (uint32_t u = 0; u < kInFlight; u++) {
+            const uint32_t i = base + u * 256 + threadIdx.x;
+            v[u] = 0.0f;
+            if (i < p.dim) asm volatile("ld.global.f32 %0, [%1];" : "=f"(v[u]) : "l"(q + i));
+        }
+#pragma unroll
+        for (uint32_t u = 0; u < kInFlight; u++) {
+            const uint32_t i = base + u * 256 + threadIdx.x;
+            if (i < p.actual_dim) {
+                const uint32_t c = i < p.dim ? u8_code(v[u], p.alpha, p.offset) : pad;
+                out[4 + i] = (uint8_t)c;
+                a1 += c;
+                a2 += c * c;
+            }
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {  // one 64-bit shared atomic per warp, not per thread (CAS loop)
