@@ -3,6 +3,7 @@
 fused scan entry points that only make sense on the GPU (score_all / search_top_k)."""
 import ctypes as C
 import sys
+import threading
 
 import numpy as np
 
@@ -17,7 +18,23 @@ class DeviceIndex:
         self.ctx = ctx
         self._L = ctx._L
         self.handle = None
+        self._tls = threading.local()
         _live_indexes.add(self)
+
+    def _topk_out(self, k):
+        """this thread's reusable output block of a host-facing top-k call, (scores, ids, n, &scores, &ids, &n), with
+        the addresses resolved once: two np.empty + two pointer look-ups per call cost more than the library's own
+        host code.  Callers return copies.  Per thread: the scoring entry points may be called from any thread."""
+        try:
+            return self._tls.out[k]
+        except AttributeError:
+            self._tls.out = {}
+        except KeyError:
+            pass
+        scores, ids, n = np.empty(k, np.float32), np.empty(k, np.uint32), C.c_uint32(0)
+        blk = (scores, ids, n, ptr(scores), ptr(ids), C.byref(n))
+        self._tls.out[k] = blk
+        return blk
 
     # ---- trait: encode_query / score_point / score_internal -------------------------------
     def encode_query(self, query):
@@ -74,12 +91,9 @@ class DeviceIndex:
         q = np.ascontiguousarray(query_f32, np.float32).reshape(-1)
         if q.size != self.vector_parameters.dim:
             raise EncodingError("ArgumentsError", f"query length {q.size} != dim {self.vector_parameters.dim}")
-        scores = np.empty(k, np.float32)
-        ids = np.empty(k, np.uint32)
-        n = C.c_uint32(0)
-        self.ctx.check(self._L.qz_search_topk(self.handle, ptr(q), k, int(bool(largest)), ptr(scores), ptr(ids),
-                                              C.byref(n)))
-        return scores[: n.value], ids[: n.value]
+        scores, ids, n, p_scores, p_ids, p_n = self._topk_out(k)
+        self.ctx.check(self._L.qz_search_topk(self.handle, ptr(q), k, int(bool(largest)), p_scores, p_ids, p_n))
+        return scores[: n.value].copy(), ids[: n.value].copy()
 
     def search_top_k_chunked(self, other, host_storage, count, query, k, largest=True):
         """out-of-core scan (qz_scan_topk_chunked): `self` and `other` are two buffer indexes of the same shape

@@ -169,18 +169,17 @@ class ShardedSearch:
         in one library call (peer mode only)"""
         if self._peer is None:
             raise RuntimeError("ShardedSearch.search needs peer=True and world > 1")
+        from .encoded_vectors import ptr
         ctx = self.index.ctx
         q = np.ascontiguousarray(query_f32, np.float32).reshape(-1)
-        scores, ids, n = np.empty(k, np.float32), np.empty(k, np.uint32), C.c_uint32(0)
+        scores, ids, n, p_scores, p_ids, p_n = self.index._topk_out(k)
         if self.root is not None:
-            ctx.check(ctx._L.qz_search_topk_gather(self.index.handle, self._peer, self.root, C.c_void_p(q.ctypes.data), k,
-                                                   int(bool(largest)), C.c_void_p(scores.ctypes.data),
-                                                   C.c_void_p(ids.ctypes.data), C.byref(n)))
-            return scores[: n.value], ids[: n.value]  # empty on the ranks that are not the root
-        ctx.check(ctx._L.qz_search_topk_peer(self.index.handle, self._peer, C.c_void_p(q.ctypes.data), k,
-                                             int(bool(largest)), C.c_void_p(scores.ctypes.data),
-                                             C.c_void_p(ids.ctypes.data), C.byref(n)))
-        return scores[: n.value], ids[: n.value]
+            ctx.check(ctx._L.qz_search_topk_gather(self.index.handle, self._peer, self.root, ptr(q), k,
+                                                   int(bool(largest)), p_scores, p_ids, p_n))
+            return scores[: n.value].copy(), ids[: n.value].copy()  # empty on the ranks that are not the root
+        ctx.check(ctx._L.qz_search_topk_peer(self.index.handle, self._peer, ptr(q), k, int(bool(largest)), p_scores,
+                                             p_ids, p_n))
+        return scores[: n.value].copy(), ids[: n.value].copy()
 
     def search_top_k(self, d_query, k, largest=True, total_count=None):
         s, i = self.search_top_k_dev(d_query, k, largest)

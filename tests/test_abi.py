@@ -80,3 +80,38 @@ def test_rust_ffi_declarations_are_current():
     rs = open(os.path.join(ROOT, "rust", "cuda_ffi.rs")).read()
     for sym in header_symbols():
         assert f"pub fn {sym}(" in rs, sym
+
+
+def test_binding_pointer_helper_and_output_blocks():
+    """ptr() must give the array's own address on the fast (buffer protocol) and the slow (read-only, strided) way;
+    the reusable top-k output block is one per thread and per k"""
+    import threading
+
+    import numpy as np
+
+    from quantization_b200._index import DeviceIndex
+    from quantization_b200.encoded_vectors import ptr
+
+    a = np.arange(64, dtype=np.float32)
+    assert ptr(a).value == a.ctypes.data
+    assert ptr(a[3:]).value == a[3:].ctypes.data
+    assert ptr(a[::2]).value == a[::2].ctypes.data          # not contiguous: slow way, same address
+    ro = np.arange(8, dtype=np.uint32)
+    ro.setflags(write=False)
+    assert ptr(ro).value == ro.ctypes.data                  # read-only: slow way
+    assert ptr(None) is None and ptr(np.empty(0, np.uint8)) is None
+
+    class Bare(DeviceIndex):
+        def __init__(self):  # no context: only the per-thread block logic is exercised
+            self._tls = threading.local()
+
+    ix = Bare()
+    mine = ix._topk_out(100)
+    assert ix._topk_out(100) is mine and ix._topk_out(10) is not mine
+    assert mine[0].dtype == np.float32 and mine[1].dtype == np.uint32 and mine[0].size == mine[1].size == 100
+    assert mine[3].value == mine[0].ctypes.data and mine[4].value == mine[1].ctypes.data
+    other = []
+    t = threading.Thread(target=lambda: other.append(ix._topk_out(100)))
+    t.start()
+    t.join()
+    assert other[0] is not mine and other[0][0] is not mine[0]
