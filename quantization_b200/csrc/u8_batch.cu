@@ -668,7 +668,7 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
         ix->soa_valid = true;
     }
     // ---- scratch arena ----
-    const uint32_t cap = k <= 256 ? 4096u : 8192u;
+    const uint32_t cap = tune_u32("QZ_BATCH_CAP", k <= 256 ? 4096u : 8192u);
     const size_t o_blob = 0, o_qcodes = o_blob + align_up((size_t)nq * (K + 4), 256);
     const size_t o_qoff = o_qcodes + align_up((size_t)nq * K, 256), o_thr = o_qoff + align_up((size_t)nq * 4, 256);
     const size_t o_cnt = o_thr + align_up((size_t)nq * 8, 256), o_ovf = o_cnt + align_up((size_t)nq * 4, 256);
@@ -703,6 +703,7 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
     for (int md = 0; md < 3; md++)
         for (int cl = 1; cl <= 2; cl++) QZ_TRY(ensure_smem_attr(ctx, (const void *)fns[md][cl], (int)kBatchSmem));
     QZ_TRY(ensure_smem_attr(ctx, (const void *)u8_batch_compact_kernel, 8192 * 8));
+    if (cap * 8 > 48 * 1024) QZ_TRY(ensure_smem_attr(ctx, (const void *)u8_batch_compact128_kernel, (int)cap * 8));
     {
         std::lock_guard<std::mutex> ga(ctx->attr_mu);
         if (!ctx->batch_cl_pick) {
@@ -768,7 +769,8 @@ static qz_status batch_search(qz_index *ix, const float *d_queries, uint32_t nq,
         uint64_t done = 0;
         // (fast schedule: the first chunk is only cap/4 rows: all of them become candidates, and the first
         // compaction sorts that many keys per query)
-        const uint64_t first = safe ? ((cap - k) / kBatchN * kBatchN ? (cap - k) / kBatchN * kBatchN : kBatchN) : cap / 4;
+        const uint64_t first = safe ? ((cap - k) / kBatchN * kBatchN ? (cap - k) / kBatchN * kBatchN : kBatchN)
+                                    : cap / tune_u32("QZ_BATCH_FIRST_DIV", 4);
         do {
             uint64_t R = first;
             if (!safe && done) {
