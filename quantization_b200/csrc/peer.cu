@@ -193,10 +193,15 @@ static qz_status search_topk_exchange(qz_index *ix, qz_peer *pe, int32_t root, c
         if (!pe->staged) QZ_CUDA(ctx, cudaEventCreateWithFlags(&pe->staged, cudaEventDisableTiming));
         QZ_CUDA(ctx, cudaEventRecord(pe->staged, ctx->stream));  // (after the kernel that reads the staged query)
         pe->staged_pending = true;
+    } else {
+        // nothing sits between the encode kernel and the scan: programmatic dependent launch, as in qz_search_topk
+        ctx->query_dep_next = ix->codec == QZ_CODEC_U8;
     }
     float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
     uint32_t *hi = reinterpret_cast<uint32_t *>(hs + k);
-    QZ_TRY(scan_topk_exchange(ix, pe, root, d_blob, k, largest, nullptr, hs, hi));
+    const qz_status scan_st = scan_topk_exchange(ix, pe, root, d_blob, k, largest, nullptr, hs, hi);
+    ctx->query_dep_next = false;
+    QZ_TRY(scan_st);
     if (root >= 0 && pe->world > 1 && (uint32_t)root != pe->rank) {  // not the root: nothing comes back
         if (n_out) *n_out = 0;
         return QZ_OK;  // (asynchronous: the launch is on the stream; the caller's next call or qz_ctx_synchronize orders it)

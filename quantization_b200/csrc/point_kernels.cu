@@ -28,6 +28,9 @@ struct U8QueryParams {
 
 __global__ void __launch_bounds__(256) u8_encode_query_kernel(U8QueryParams p) {
     __shared__ unsigned long long s1, s2;
+    // a scan launched behind this kernel as its programmatic dependent (qz_search_topk) may start setting up now; it
+    // waits for this grid before it reads the encoded query.  No effect on ordinary launches.
+    asm volatile("griddepcontrol.launch_dependents;");
     const float *q = p.queries + (size_t)blockIdx.x * p.dim;
     uint8_t *out = p.out + (size_t)blockIdx.x * (p.actual_dim + 4);
     if (threadIdx.x == 0) s1 = s2 = 0;

@@ -247,10 +247,14 @@ qz_status qz_search_topk(qz_index *ix, const float *query, uint32_t k, int32_t l
     if (fb && qb) {
         memcpy(ctx->h_pin, query, fb);
         QZ_TRY(qz_encode_query_dev(ix, reinterpret_cast<const float *>(ctx->h_pin), 1, d_blob));
+        // the scan is launched as the programmatic dependent of the encode kernel (u8: the kernel that triggers early)
+        ctx->query_dep_next = ix->codec == QZ_CODEC_U8;
     }
     float *hs = reinterpret_cast<float *>(ctx->h_pin + fb_pad);
     uint32_t *hi = reinterpret_cast<uint32_t *>(hs + k);
-    QZ_TRY(qz_scan_topk_dev(ix, d_blob, k, largest, nullptr, hs, hi));
+    const qz_status scan_st = qz_scan_topk_dev(ix, d_blob, k, largest, nullptr, hs, hi);
+    ctx->query_dep_next = false;
+    QZ_TRY(scan_st);
     QZ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const uint32_t m = (uint32_t)(ix->count < k ? ix->count : k);
     memcpy(scores, hs, (size_t)m * 4);

@@ -48,6 +48,8 @@ struct qz_ctx {
     bool chain_ok = false;      // caller's promise for a stream the context does not own
     uint64_t chain_tail = 0;    // value of `launches` right after the last chainable scan launch, 0 = none
     uint64_t scan_seq = 0;      // fused scans launched with a tile counter (picks one of the two counters)
+    bool query_dep_next = false;  // set by the host-facing search entry points right after their query-encode launch:
+                                  // the next row scan is launched as its programmatic dependent (RowScanParams::query_dep)
     bool pdl_next = false;      // launch_one: give the next launch the programmatic-serialization attribute
     uint64_t *d_stamps = nullptr;  // qz_ctx_set_phase_stamps: [sm_count][QZ_STAMP_WORDS], or NULL
     uint64_t timed_n = 0;

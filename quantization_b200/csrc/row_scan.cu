@@ -184,6 +184,13 @@ qz_status launch_row_scan(qz_index *ix, const void *d_query, float *d_scores, ui
     // griddepcontrol.wait (query and storage are inputs of both), so only the tail of the previous scan overlaps.
     const bool chainable = fin && *fin->fused && !ctx->timing && (ctx->own_stream || ctx->chain_ok);
     ctx->pdl_next = chainable && ctx->chain_tail != 0 && ctx->chain_tail == ctx->launches;
+    // host-facing search: the query-encode kernel is the previous launch on the stream and triggers its dependents at
+    // once, so this kernel's set-up and first bulk copies overlap it (nothing but events may sit between the two)
+    if (ctx->query_dep_next && !ctx->timing && !ctx->d_stamps) {
+        p.query_dep = 1;
+        ctx->pdl_next = true;
+    }
+    ctx->query_dep_next = false;
     cudaError_t e;
     timing_begin(ctx);
     if (ix->codec == QZ_CODEC_BIN && pl.vec) e = launch_row_scan_xorv(ctx, pl.lpr, pl.wpl, pl.full, p, grid, pl.smem);

@@ -68,6 +68,10 @@ struct RowScanParams {
     MergeParams merge;
     PeerExchange px;  // px.world > 1: merge.keys points at this GPU's own gather slot; see PeerExchange
     uint64_t *stamps;  // optional [gridDim.x][QZ_STAMP_WORDS] phase stamps (qz_ctx_set_phase_stamps)
+    // 1 = the query is written by the kernel launched just before this one on the stream (the host-facing search: query
+    // encode -> scan) and this launch is its programmatic dependent: the CTAs set up and the ring starts filling
+    // while the encode kernel runs; the consumers wait for it before they read the query
+    uint32_t query_dep;
     // Tile schedule.  Local tile t of a CTA is global tile blockIdx.x + t * gridDim.x while t < n_static (one ring's
     // worth: they are issued while the first draw is in flight); later
     // tiles are drawn from a device-wide counter (global tile gridDim.x * n_static + ticket), a few at a time,
@@ -211,20 +215,21 @@ __global__ void __launch_bounds__(kScanThreads, 1) row_scan_kernel(const RowScan
     constexpr int kQ = kVec ? 4 * WPL : WPL;  // query words a lane keeps in registers
     uint32_t q[kQ];
     bool jv[WPL];
+    if (p.query_dep) asm volatile("griddepcontrol.wait;" ::: "memory");
 #pragma unroll
     for (int j = 0; j < WPL; j++) {
         if (kVec) {
             const uint32_t v = lsub + kLpr * j;  // 16-byte vector of the row this lane owns
             jv[j] = FULL || 4 * v < p.code_words;
 #pragma unroll
-            for (int c = 0; c < 4; c++) q[(4 * j + c) % kQ] = jv[j] ? __ldg(p.query + 4 * v + c) : 0u;
+            for (int c = 0; c < 4; c++) q[(4 * j + c) % kQ] = jv[j] ? __ldcg(p.query + 4 * v + c) : 0u;
         } else {
             const uint32_t w = lane + 32 * j;
             jv[j] = FULL || w < p.code_words;
-            q[j] = jv[j] ? __ldg(p.query + p.hdr_words + w) : 0u;
+            q[j] = jv[j] ? __ldcg(p.query + p.hdr_words + w) : 0u;
         }
     }
-    const float q_off = p.hdr_words ? __uint_as_float(__ldg(p.query)) : 0.0f;
+    const float q_off = p.hdr_words ? __uint_as_float(__ldcg(p.query)) : 0.0f;
 
     CtaTopK st{top, thr, lock, p.k, p.Kp};
     uint64_t *cand = cand_all + warp * kCandPerWarp;
