@@ -223,7 +223,7 @@ qz_status pq_scan(qz_index *ix, const void *d_lut, float *d_scores, uint32_t k, 
         return launch_scores_topk(ctx, (const float *)ctx->d_io, 1, 0, ix->count, d_scores, k, largest, ix->id_base,
                                   n_lists, Kp_out);
     }
-    dim3 pg(8, slices);
+    dim3 pg(32, slices);  // 4 LUT entries per thread (the kernel is latency-bound: 8 blocks per slice took 5 us)
     pq_lut_permute_kernel<<<pg, 256, 0, ctx->stream>>>((const float *)d_lut, ix->n_chunks, ix->d_lut_perm);
     QZ_TRY(check_launch(ctx, "pq_lut_permute_kernel"));
     // streaming kernel (pq_scan2.cu): k <= 128 is reduced inside the kernel; otherwise the final scores go to
