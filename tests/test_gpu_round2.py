@@ -264,6 +264,29 @@ def test_two_threads_share_one_context(ctx):
     b.close()
 
 
+def test_search_reads_the_query_of_this_call(ctx):
+    """qz_search_topk launches the scan as the programmatic dependent of the query-encode kernel: the scan's CTAs are
+    resident, streaming tiles, before the encoded query exists, and must not score a row until it does.  A stream of
+    calls with a DIFFERENT query each (same staging buffers every time) must give, call by call, what encode_query +
+    search_top_k give for that query (two separate synchronised calls: no overlap) -- a scan that picked up the
+    previous call's encoded query would return the previous call's answer.  Sized so that every SM has a CTA and the
+    tile counter is on (the C2 kernel variant: 1536-d)."""
+    count, dim, k = 300_000, 1536, 100
+    rng = np.random.default_rng(77)
+    data = rng.random((count, dim), dtype=np.float32)
+    vp = qz.VectorParameters(dim, count, qz.DistanceType.Dot, False)
+    g = qz.EncodedVectorsU8.encode(data, qz.VecStorageBuilder(), vp, None, ctx=ctx)
+    queries = rng.random((12, dim), dtype=np.float32)
+    queries[5] = -queries[4]           # an answer far away from its predecessor's
+    want = [g.search_top_k(g.encode_query(q), k, True) for q in queries]
+    assert len({tuple(w[1][:5]) for w in want}) > 6  # the queries really have different answers
+    for rep in range(5):
+        for q, (ws, wi) in zip(queries, want):
+            s, i = g.search(q, k, True)
+            assert np.array_equal(i, wi) and np.array_equal(bits(s), bits(ws)), rep
+    g.close()
+
+
 def test_two_contexts_on_two_devices_in_one_process():
     """qz_ctx_create(device, ...) twice in one process (the natural single-process multi-GPU host): every kernel's
     shared-memory opt-in is per device, so the second device must get it too (round-1 defect: process-wide statics)"""
